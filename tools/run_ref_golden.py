@@ -1,0 +1,26 @@
+"""Run the reference CUDA build (oracle/_ref/ref_driver) over tools/golden_cases.py on a GPU
+box and leave the outputs in gpurun_out/golden/.  TEST INFRASTRUCTURE.
+
+    gpurun -- python tools/run_ref_golden.py
+"""
+import os, subprocess, sys, json
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from tools import golden_cases as gc
+
+ROOT = os.path.dirname(gc.HERE)
+OUT = os.path.join(ROOT, "gpurun_out", "golden")
+os.makedirs(OUT, exist_ok=True)
+drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+log = {}
+only = sys.argv[1:]
+for case, (img, flags, planes) in gc.CASES.items():
+    if only and case not in only:
+        continue
+    w, h, _ = gc.IMAGES[img]
+    cmd = [drv, "--in", gc.image_path(img), "--w", str(w), "--h", str(h), "--out", os.path.join(OUT, case)] + flags
+    if planes:
+        cmd += ["--dump-planes", "--dump-tables"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    log[case] = {"rc": r.returncode, "stdout": r.stdout.strip(), "stderr": r.stderr.strip()[-400:]}
+    print(case, r.returncode, r.stdout.strip(), r.stderr.strip()[-200:], flush=True)
+json.dump(log, open(os.path.join(OUT, "log.json"), "w"), indent=1)
