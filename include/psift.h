@@ -1,0 +1,140 @@
+/*
+ * psift.h -- C ABI of the B200-native SIFT extraction path (libpopsift_b200.so).
+ *
+ * Plain pointers and sizes only.  This is the boundary a foreign-language binding
+ * (ctypes, cgo, JNI ...) or the C++ drop-in classes in <popsift/popsift.h> call.
+ * Each entry point names the reference interface it stands in for
+ * (paths relative to the reference tree, /root/reference).
+ *
+ * Error convention: every int-returning function returns PSIFT_OK (0) or a negative
+ * PSIFT_E_* code; psift_last_error() returns a thread-local message.  Nothing in
+ * this library calls exit() (the reference does: common/debug_macros.h:119-146).
+ * There is no CPU fallback: without a CUDA device psift_create fails.
+ */
+#ifndef PSIFT_H
+#define PSIFT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PSIFT_OK            0
+#define PSIFT_E_INVALID    -1   /* bad argument / unsupported config */
+#define PSIFT_E_CUDA       -2   /* CUDA runtime error (message has the detail) */
+#define PSIFT_E_NODEVICE   -3
+#define PSIFT_E_STATE      -4   /* call order violated */
+
+#define PSIFT_MAX_OCTAVES  20   /* reference sift_conf.h:13 MAX_OCTAVES */
+#define PSIFT_MAX_ORI       4   /* reference sift_constants.h:51 ORIENTATION_MAX_COUNT */
+
+/* enums mirror popsift::Config (reference sift_conf.h:28-120) value for value */
+enum { PSIFT_GAUSS_VLFEAT_COMPUTE = 0, PSIFT_GAUSS_VLFEAT_RELATIVE = 1, PSIFT_GAUSS_VLFEAT_RELATIVE_ALL = 2,
+       PSIFT_GAUSS_OPENCV_COMPUTE = 3, PSIFT_GAUSS_FIXED9 = 4, PSIFT_GAUSS_FIXED15 = 5 };
+enum { PSIFT_MODE_POPSIFT = 0, PSIFT_MODE_OPENCV = 1, PSIFT_MODE_VLFEAT = 2 };
+enum { PSIFT_DESC_LOOP = 0, PSIFT_DESC_ILOOP = 1, PSIFT_DESC_GRID = 2, PSIFT_DESC_IGRID = 3, PSIFT_DESC_NOTILE = 4 };
+enum { PSIFT_NORM_ROOTSIFT = 0, PSIFT_NORM_CLASSIC = 1 };
+enum { PSIFT_FILTER_RANDOM = 0, PSIFT_FILTER_LARGEST_FIRST = 1, PSIFT_FILTER_SMALLEST_FIRST = 2 };
+
+/* POD mirror of the state of popsift::Config (reference sift_conf.h:270-320, defaults
+ * sift_conf.cu:17-40).  psift_config_default() fills the reference defaults. */
+typedef struct psift_config {
+    int   octaves;              /* -1: derive from the image size (popsift.cpp:107-111) */
+    int   levels;               /* 3 */
+    float sigma;                /* 1.6 */
+    float edge_limit;           /* 10 */
+    float threshold;            /* 0.04 */
+    float upscale_factor;       /* 1: input is upscaled by 2^upscale_factor (= -downsampling) */
+    int   gauss_mode;           /* PSIFT_GAUSS_* */
+    int   sift_mode;            /* PSIFT_MODE_* */
+    int   desc_mode;            /* PSIFT_DESC_* */
+    int   norm_mode;            /* PSIFT_NORM_* */
+    int   norm_multi;           /* descriptors are scaled by 2^norm_multi */
+    int   max_extrema;          /* 100000 per octave */
+    int   filter_max_extrema;   /* -1: no grid filter */
+    int   filter_grid_size;     /* 2 */
+    int   filter_sorting;       /* PSIFT_FILTER_* */
+    int   assume_initial_blur;  /* 1 */
+    float initial_blur;         /* 0.5 */
+    int   deterministic_order;  /* 1: features come back sorted (octave, level, y, x) -- an extension;
+                                   the reference's order is whatever its atomics produced */
+} psift_config;
+
+/* One returned keypoint: field for field popsift::Feature (reference features.h:22-35), with
+ * descriptor INDICES instead of pointers so that the record is position independent. */
+typedef struct psift_feature {
+    int   debug_octave;
+    float xpos, ypos, sigma;             /* input-image coordinates */
+    int   num_ori;
+    float orientation[PSIFT_MAX_ORI];
+    int   desc_idx[PSIFT_MAX_ORI];       /* index into psift_result.desc (units of 128 floats); -1 if unused */
+} psift_feature;
+
+/* Internal keypoint record in octave coordinates (reference sift_extremum.h:37-49 Extremum);
+ * exposed for parity checks of the integer fields (octave, lpos). */
+typedef struct psift_extremum {
+    float xpos, ypos;
+    int   lpos;
+    float sigma;
+    int   octave, num_ori, idx_ori;
+    float orientation[PSIFT_MAX_ORI];
+} psift_extremum;
+
+typedef struct psift_result {
+    int                  n_feat;
+    int                  n_desc;
+    const psift_feature* feat;        /* n_feat records, pinned host memory owned by the job */
+    const float*         desc;        /* n_desc x 128 floats */
+    const psift_extremum* ext;        /* n_feat records (octave coordinates) */
+    int                  ext_ct[PSIFT_MAX_OCTAVES];   /* keypoints per octave */
+    int                  ori_ct[PSIFT_MAX_OCTAVES];   /* descriptors per octave */
+    int                  n_octaves;
+    int                  n_levels;                     /* Gaussian levels per octave = levels+3 */
+    int                  w0, h0;                       /* octave-0 size */
+} psift_result;
+
+typedef struct psift_ctx psift_ctx;
+typedef struct psift_job psift_job;
+
+void        psift_config_default( psift_config* cfg );              /* popsift::Config::Config(), sift_conf.cu:17-40 */
+const char* psift_last_error( void );
+int         psift_device_count( void );                              /* common/device_prop.cu:28-50 */
+
+/* PopSift::PopSift + configure (popsift.cpp:16-87): bind to a CUDA device, build the Gauss and
+ * descriptor tables (gauss_filter.cu:127-257, sift_constants.cu:22-53). */
+int  psift_create( int device, const psift_config* cfg, psift_ctx** out );
+int  psift_configure( psift_ctx* ctx, const psift_config* cfg );    /* PopSift::configure, popsift.cpp:63-87 */
+void psift_destroy( psift_ctx* ctx );                               /* PopSift::uninit, popsift.cpp:122-137 */
+
+/* PopSift::enqueue (popsift.cpp:139-169) + the worker's step1/step2/get_descriptors
+ * (popsift.cpp:182-213).  The image is copied before the call returns (popsift.cpp:245-247).
+ * The work is queued on the context's streams; psift_wait blocks until the features are on the host. */
+int  psift_submit_u8 ( psift_ctx* ctx, int w, int h, const uint8_t* host, size_t pitch_bytes, psift_job** out );
+int  psift_submit_f32( psift_ctx* ctx, int w, int h, const float*   host, size_t pitch_bytes, psift_job** out );
+/* same, input already resident in device memory (no H2D inside) */
+int  psift_submit_dev_u8( psift_ctx* ctx, int w, int h, const uint8_t* dev, size_t pitch_bytes, psift_job** out );
+int  psift_wait( psift_job* job, psift_result* out );               /* SiftJob::get, popsift.cpp:300-313 */
+void psift_job_free( psift_job* job );                              /* delete SiftJob */
+
+/* Parity / profiling hooks (the reference's LogMode::All dumps, sift_octave.cu:110-187). Valid after
+ * psift_wait and before the next submit on the same context slot. */
+int  psift_octave_size( psift_ctx* ctx, int octave, int* w, int* h );
+int  psift_debug_read_level( psift_ctx* ctx, int octave, int level, float* host_out );   /* Gaussian level, w*h floats */
+int  psift_debug_read_dog  ( psift_ctx* ctx, int octave, int level, float* host_out );   /* G[level+1]-G[level] */
+/* Gauss tables exactly as uploaded: which = 0 inc, 1 abs_o0, 2 abs_oN, 3 dd; 32 taps per level */
+int  psift_debug_gauss_table( psift_ctx* ctx, int which, int level, float* filter32, float* sigma, int* span );
+int  psift_debug_desc_tables( psift_ctx* ctx, float* desc_gauss_1600, float* desc_tile_16 );
+
+/* Device-side timing of the last finished job on this context, milliseconds (CUDA events on
+ * the context's stream): [0] upload, [1] pyramid, [2] extrema, [3] orientation, [4] descriptor+norm,
+ * [5] download, [6] total.  For bench.py's roofline figures. */
+int  psift_last_timing( psift_ctx* ctx, float ms[8] );
+/* number of kernels this library launched since the context was created */
+long long psift_launch_count( psift_ctx* ctx );
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PSIFT_H */

@@ -12,7 +12,11 @@
  *   - golden outputs for parity tests (features, descriptors, Gaussian/DoG planes)
  *   - the timed "reference arm" of bench.py (--impl reference).
  */
+/* test infrastructure only: reach the per-stage entry points (find_extrema, orientation,
+ * descriptors are private in the reference's Pyramid, sift_pyramid.h:118-170) */
+#define private public
 #include "popsift/sift_pyramid.h"
+#undef private
 #include "popsift/sift_octave.h"
 #include "popsift/s_image.h"
 #include "popsift/gauss_filter.h"
@@ -31,6 +35,8 @@
 #include <algorithm>
 
 using namespace popsift;
+
+namespace popsift { __global__ void ori_par( const int octave, const int ext_ct_prefix_sum, cudaTextureObject_t layer, const int w, const int h ); }
 
 static void die( const char* msg ) { fprintf( stderr, "ref_driver: %s\n", msg ); exit( 2 ); }
 
@@ -118,8 +124,8 @@ int main( int argc, char** argv )
 {
     std::vector<std::string> inputs;
     std::string out_prefix;
-    int w = 0, h = 0, iters = 1, warmup = 0;
-    bool dump_planes = false, float_mode = false, tables = false;
+    int w = 0, h = 0, iters = 1, warmup = 0, ori_o = -1, ori_i = 0;
+    bool dump_planes = false, float_mode = false, tables = false, debug_stages = false;
 
     cudaSetDevice( 0 );
     Config conf;
@@ -136,6 +142,8 @@ int main( int argc, char** argv )
         else if( a == "--dump-planes" ) dump_planes = true;
         else if( a == "--float-mode" )  float_mode = true;
         else if( a == "--dump-tables" ) tables = true;
+        else if( a == "--debug-stages" ) debug_stages = true;
+        else if( a == "--ori-one" ) { debug_stages = true; ori_o = atoi( next() ); ori_i = atoi( next() ); }
         else if( a == "--mode" ) {
             std::string m = next();
             if( m == "popsift" ) conf.setMode( Config::PopSift );
@@ -204,6 +212,42 @@ int main( int argc, char** argv )
         img->resetDimensions( w, h );          /* SiftJob::setImg */
         img->load( im.data() );
         pyr->step1( conf, img );
+        if( debug_stages ) {
+            auto chk = [&]( const char* what ) {
+                cudaError_t e = cudaDeviceSynchronize();
+                if( e == cudaSuccess ) e = cudaGetLastError();
+                fprintf( stderr, "stage %-12s : %s\n", what, cudaGetErrorString( e ) );
+                if( e != cudaSuccess ) exit( 4 );
+            };
+            chk( "pyramid" );
+            pyr->find_extrema( conf ); chk( "find_extrema" );
+            ExtremaCounters c; cudaMemcpyFromSymbol( &c, dct, sizeof(c) );
+            for( int o = 0; o < conf.octaves; o++ ) {
+                int n = c.ext_ct[o];
+                std::vector<int> off( std::max( n, 1 ) ); std::vector<InitialExtremum> ie( std::max( n, 1 ) );
+                cudaMemcpy( off.data(), dobuf_shadow.i_ext_off[o], n * sizeof(int), cudaMemcpyDeviceToHost );
+                cudaMemcpy( ie.data(), dobuf_shadow.i_ext_dat[o], n * sizeof(InitialExtremum), cudaMemcpyDeviceToHost );
+                int bad = 0; for( int i = 0; i < n; i++ ) if( off[i] < 0 || off[i] >= n ) bad++;
+                fprintf( stderr, "  octave %d: ext_ct %d, bad i_ext_off %d", o, n, bad );
+                for( int i = 0; i < std::min( n, 3 ); i++ ) fprintf( stderr, " | off %d x %.2f y %.2f l %d s %.3f", off[i], ie[i].xpos, ie[i].ypos, ie[i].lpos, ie[i].sigma );
+                fprintf( stderr, "\n" );
+            }
+            if( ori_o >= 0 ) {
+                /* run the reference's ori_par on ONE extremum (fault bisection) */
+                int one = ori_i;
+                cudaMemcpy( dobuf_shadow.i_ext_off[ori_o], &one, sizeof(int), cudaMemcpyHostToDevice );
+                ExtremaCounters c1 = c; c1.ext_ct[ori_o] = 1;
+                cudaMemcpyToSymbol( dct, &c1, sizeof(c1) );
+                Octave& oc = pyr->getOctave( ori_o );
+                popsift::ori_par<<< 1, 32 >>>( ori_o, 0, oc.getDataTexPoint(), oc.getWidth(), oc.getHeight() );
+                chk( "ori_par(one)" );
+                Extremum e; cudaMemcpy( &e, dobuf_shadow.extrema, sizeof(e), cudaMemcpyDeviceToHost );
+                fprintf( stderr, "  -> num_ori %d ori %.5f %.5f %.5f %.5f\n", e.num_ori, e.orientation[0], e.orientation[1], e.orientation[2], e.orientation[3] );
+                exit( 0 );
+            }
+            pyr->orientation( conf );  chk( "orientation" );
+            pyr->descriptors( conf );  chk( "descriptors" );
+        } else
         pyr->step2( conf );
         FeaturesHost* fh = pyr->get_descriptors( conf );
         cudaDeviceSynchronize();

@@ -20,7 +20,10 @@ for case, (img, flags, planes) in gc.CASES.items():
     cmd = [drv, "--in", gc.image_path(img), "--w", str(w), "--h", str(h), "--out", os.path.join(OUT, case)] + flags
     if planes:
         cmd += ["--dump-planes", "--dump-tables"]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=20)
+    except subprocess.TimeoutExpired:
+        print(case, "TIMEOUT", flush=True); log[case] = {"rc": -9}; continue
     log[case] = {"rc": r.returncode, "stdout": r.stdout.strip(), "stderr": r.stderr.strip()[-400:]}
     print(case, r.returncode, r.stdout.strip(), r.stderr.strip()[-200:], flush=True)
 json.dump(log, open(os.path.join(OUT, "log.json"), "w"), indent=1)
