@@ -1,0 +1,28 @@
+# Builds libpopsift_b200.so (C ABI + the C++ drop-in classes) for sm_100a, in-tree.
+NVCC   ?= nvcc
+ARCH   := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -ffp-contract=off -Iinclude
+CSRC   := popsift_b200/csrc
+OBJDIR := build/obj
+LIB    := popsift_b200/libpopsift_b200.so
+
+CU_SRCS  := $(CSRC)/k_pyramid.cu $(CSRC)/k_extrema.cu $(CSRC)/k_orient.cu $(CSRC)/k_desc.cu $(CSRC)/pipeline.cu
+CPP_SRCS := $(CSRC)/tables.cpp $(wildcard $(CSRC)/host/*.cpp)
+OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU_SRCS)) $(patsubst $(CSRC)/%.cpp,$(OBJDIR)/%.o,$(CPP_SRCS))
+
+all: $(LIB)
+
+$(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/common.h $(CSRC)/kernels.h include/psift.h
+	@mkdir -p $(dir $@)
+	$(NVCC) $(NVFLAGS) -c -o $@ $<
+
+$(OBJDIR)/%.o: $(CSRC)/%.cpp $(CSRC)/common.h include/psift.h
+	@mkdir -p $(dir $@)
+	$(NVCC) $(NVFLAGS) -c -o $@ $<
+
+$(LIB): $(OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart
+
+clean:
+	rm -rf build $(LIB)
+.PHONY: all clean

@@ -123,9 +123,13 @@ void psift_job_free( psift_job* job );                              /* delete Si
 int  psift_octave_size( psift_ctx* ctx, int octave, int* w, int* h );
 int  psift_debug_read_level( psift_ctx* ctx, int octave, int level, float* host_out );   /* Gaussian level, w*h floats */
 int  psift_debug_read_dog  ( psift_ctx* ctx, int octave, int level, float* host_out );   /* G[level+1]-G[level] */
-/* Gauss tables exactly as uploaded: which = 0 inc, 1 abs_o0, 2 abs_oN, 3 dd; 32 taps per level */
-int  psift_debug_gauss_table( psift_ctx* ctx, int which, int level, float* filter32, float* sigma, int* span );
-int  psift_debug_desc_tables( psift_ctx* ctx, float* desc_gauss_1600, float* desc_tile_16 );
+/* Host-only table builders (no device needed): the Gauss tables exactly as they are uploaded
+ * (gauss_filter.cu:127-257): which = 0 inc, 1 abs_o0, 2 abs_oN, 3 dd; 32 taps per level; and the
+ * scalar/descriptor constants (sift_constants.cu:22-53): scalars = sigma_k, threshold. */
+int  psift_debug_gauss_table( const psift_config* cfg, int which, int level, float* filter32, float* sigma, int* span );
+int  psift_debug_desc_tables( const psift_config* cfg, float* desc_gauss_1600, float* desc_tile_16, float* scalars2 );
+/* octave-0 size and octave count for an input size (popsift.cpp:89-120) */
+int  psift_pyramid_geometry( const psift_config* cfg, int w, int h, int* w0, int* h0, int* n_octaves );
 
 /* Device-side timing of the last finished job on this context, milliseconds (CUDA events on
  * the context's stream): [0] upload, [1] pyramid, [2] extrema, [3] orientation, [4] descriptor+norm,

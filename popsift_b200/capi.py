@@ -1,0 +1,225 @@
+"""ctypes binding of the C ABI in include/psift.h (libpopsift_b200.so).
+
+This is plumbing for tests and bench.py; the product is the shared library.  Nothing here
+computes: if the library (or a CUDA device) is missing the calls raise.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpopsift_b200.so")
+
+MAX_OCT = 20
+MAX_ORI = 4
+
+
+class Config(C.Structure):
+    _fields_ = [("octaves", C.c_int), ("levels", C.c_int), ("sigma", C.c_float), ("edge_limit", C.c_float),
+                ("threshold", C.c_float), ("upscale_factor", C.c_float), ("gauss_mode", C.c_int),
+                ("sift_mode", C.c_int), ("desc_mode", C.c_int), ("norm_mode", C.c_int), ("norm_multi", C.c_int),
+                ("max_extrema", C.c_int), ("filter_max_extrema", C.c_int), ("filter_grid_size", C.c_int),
+                ("filter_sorting", C.c_int), ("assume_initial_blur", C.c_int), ("initial_blur", C.c_float),
+                ("deterministic_order", C.c_int)]
+
+
+FEATURE_DTYPE = np.dtype([("octave", "<i4"), ("x", "<f4"), ("y", "<f4"), ("sigma", "<f4"), ("num_ori", "<i4"),
+                          ("ori", "<f4", (4,)), ("desc_idx", "<i4", (4,))])
+EXTREMUM_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("lpos", "<i4"), ("sigma", "<f4"), ("octave", "<i4"),
+                           ("num_ori", "<i4"), ("idx_ori", "<i4"), ("ori", "<f4", (4,))])
+
+
+class Result(C.Structure):
+    _fields_ = [("n_feat", C.c_int), ("n_desc", C.c_int), ("feat", C.c_void_p), ("desc", C.c_void_p),
+                ("ext", C.c_void_p), ("ext_ct", C.c_int * MAX_OCT), ("ori_ct", C.c_int * MAX_OCT),
+                ("n_octaves", C.c_int), ("n_levels", C.c_int), ("w0", C.c_int), ("h0", C.c_int)]
+
+
+GAUSS = {"vlfeat": 0, "vlfeat-hw-interpolated": 1, "relative": 1, "vlfeat-direct": 2, "opencv": 3, "fixed9": 4, "fixed15": 5}
+MODE = {"popsift": 0, "opencv": 1, "vlfeat": 2}
+DESC = {"loop": 0, "iloop": 1, "grid": 2, "igrid": 3, "notile": 4}
+NORM = {"RootSift": 0, "classic": 1}
+FSORT = {"random": 0, "up": 1, "down": 2}
+
+EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "psift_create", "psift_configure",
+           "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_wait",
+           "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
+           "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
+           "psift_launch_count"]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libpopsift_b200.so is not built: run `make` (or __graft_entry__.build()) first")
+        L = C.CDLL(LIB_PATH)
+        L.psift_last_error.restype = C.c_char_p
+        L.psift_launch_count.restype = C.c_longlong
+        L.psift_launch_count.argtypes = [C.c_void_p]
+        L.psift_create.argtypes = [C.c_int, C.POINTER(Config), C.POINTER(C.c_void_p)]
+        L.psift_configure.argtypes = [C.c_void_p, C.POINTER(Config)]
+        L.psift_destroy.argtypes = [C.c_void_p]
+        L.psift_submit_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.psift_submit_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.psift_submit_dev_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.psift_wait.argtypes = [C.c_void_p, C.POINTER(Result)]
+        L.psift_job_free.argtypes = [C.c_void_p]
+        L.psift_octave_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.psift_debug_read_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.psift_debug_read_dog.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.psift_debug_gauss_table.argtypes = [C.POINTER(Config), C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+        L.psift_debug_desc_tables.argtypes = [C.POINTER(Config), C.c_void_p, C.c_void_p, C.c_void_p]
+        L.psift_pyramid_geometry.argtypes = [C.POINTER(Config), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.psift_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        _lib = L
+    return _lib
+
+
+class PsiftError(RuntimeError):
+    pass
+
+
+def _chk(rc):
+    if rc != 0:
+        raise PsiftError("psift error %d: %s" % (rc, lib().psift_last_error().decode()))
+
+
+def default_config(**kw):
+    """psift_config with the reference defaults; keyword arguments use the reference's spellings
+    (mode='vlfeat', gauss_mode='opencv', desc_mode='igrid', norm_mode='classic', downsampling=-1 ...)."""
+    cfg = Config()
+    lib().psift_config_default(C.byref(cfg))
+    for k, v in kw.items():
+        if k == "mode": cfg.sift_mode = MODE[v]
+        elif k == "gauss_mode": cfg.gauss_mode = GAUSS[v]
+        elif k == "desc_mode": cfg.desc_mode = DESC[v]
+        elif k == "norm_mode": cfg.norm_mode = NORM[v]
+        elif k == "filter_sort": cfg.filter_sorting = FSORT[v]
+        elif k == "downsampling": cfg.upscale_factor = -float(v)
+        elif k == "initial_blur":
+            cfg.initial_blur = float(v); cfg.assume_initial_blur = 0 if v == 0 else 1
+        elif hasattr(cfg, k): setattr(cfg, k, v)
+        else: raise KeyError(k)
+    return cfg
+
+
+def config_from_flags(flags):
+    """Translate ref_driver / popsift-demo style flags (tools/golden_cases.py) into a psift_config."""
+    kw = {}
+    it = iter(flags)
+    for f in it:
+        v = next(it)
+        key = f.lstrip("-").replace("-", "_")
+        if key in ("mode", "gauss_mode", "desc_mode", "norm_mode", "filter_sort"): kw[key] = v
+        elif key == "downsampling": kw["downsampling"] = float(v)
+        elif key in ("octaves", "levels", "norm_multi", "filter_max_extrema"): kw[key] = int(v)
+        elif key == "filter_grid": kw["filter_grid_size"] = int(v)
+        elif key in ("sigma", "threshold", "initial_blur"): kw[key] = float(v)
+        elif key == "edge_threshold": kw["edge_limit"] = float(v)
+        else: raise KeyError(f)
+    return default_config(**kw)
+
+
+class Extraction:
+    """Features of one image, copied out of the job's pinned buffers."""
+    def __init__(self, r):
+        self.n_feat, self.n_desc = r.n_feat, r.n_desc
+        self.feat = np.ctypeslib.as_array(C.cast(r.feat, C.POINTER(C.c_uint8)), (r.n_feat * FEATURE_DTYPE.itemsize,)).view(FEATURE_DTYPE).copy() if r.n_feat else np.zeros(0, FEATURE_DTYPE)
+        self.ext = np.ctypeslib.as_array(C.cast(r.ext, C.POINTER(C.c_uint8)), (r.n_feat * EXTREMUM_DTYPE.itemsize,)).view(EXTREMUM_DTYPE).copy() if r.n_feat else np.zeros(0, EXTREMUM_DTYPE)
+        self.desc = np.ctypeslib.as_array(C.cast(r.desc, C.POINTER(C.c_float)), (r.n_desc, 128)).copy() if r.n_desc else np.zeros((0, 128), np.float32)
+        self.ext_ct = np.array(r.ext_ct[:], dtype=np.int32)
+        self.ori_ct = np.array(r.ori_ct[:], dtype=np.int32)
+        self.n_octaves, self.n_levels, self.w0, self.h0 = r.n_octaves, r.n_levels, r.w0, r.h0
+
+
+class Context:
+    """One extraction context on one CUDA device (psift_create / psift_destroy)."""
+    def __init__(self, cfg=None, device=0):
+        self._h = C.c_void_p()
+        cfg = cfg if cfg is not None else default_config()
+        _chk(lib().psift_create(device, C.byref(cfg), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().psift_destroy(self._h); self._h = C.c_void_p()
+
+    def __enter__(self): return self
+    def __exit__(self, *a): self.close()
+
+    def configure(self, cfg):
+        _chk(lib().psift_configure(self._h, C.byref(cfg)))
+
+    def submit(self, img):
+        img = np.ascontiguousarray(img)
+        h, w = img.shape
+        job = C.c_void_p()
+        if img.dtype == np.uint8:
+            _chk(lib().psift_submit_u8(self._h, w, h, img.ctypes.data, w, C.byref(job)))
+        elif img.dtype == np.float32:
+            _chk(lib().psift_submit_f32(self._h, w, h, img.ctypes.data, w * 4, C.byref(job)))
+        else:
+            raise TypeError("image must be uint8 or float32")
+        return job
+
+    def submit_dev_u8(self, ptr, w, h, pitch):
+        job = C.c_void_p()
+        _chk(lib().psift_submit_dev_u8(self._h, w, h, C.c_void_p(ptr), pitch, C.byref(job)))
+        return job
+
+    def wait(self, job, copy=True):
+        r = Result()
+        _chk(lib().psift_wait(job, C.byref(r)))
+        return Extraction(r) if copy else (r.n_feat, r.n_desc)
+
+    def free(self, job):
+        lib().psift_job_free(job)
+
+    def extract(self, img):
+        job = self.submit(img)
+        try:
+            return self.wait(job)
+        finally:
+            self.free(job)
+
+    def level(self, octave, level):
+        w, h = C.c_int(), C.c_int()
+        _chk(lib().psift_octave_size(self._h, octave, C.byref(w), C.byref(h)))
+        out = np.empty((h.value, w.value), np.float32)
+        _chk(lib().psift_debug_read_level(self._h, octave, level, out.ctypes.data))
+        return out
+
+    def dog(self, octave, level):
+        w, h = C.c_int(), C.c_int()
+        _chk(lib().psift_octave_size(self._h, octave, C.byref(w), C.byref(h)))
+        out = np.empty((h.value, w.value), np.float32)
+        _chk(lib().psift_debug_read_dog(self._h, octave, level, out.ctypes.data))
+        return out
+
+    def timing(self):
+        ms = (C.c_float * 8)()
+        _chk(lib().psift_last_timing(self._h, ms))
+        return dict(zip(["upload", "pyramid", "extrema", "orientation", "descriptor", "download", "total"], [float(x) for x in ms[:7]]))
+
+    def launch_count(self):
+        return int(lib().psift_launch_count(self._h))
+
+
+def gauss_table(cfg, which, level):
+    f = np.zeros(32, np.float32); s = C.c_float(); sp = C.c_int()
+    _chk(lib().psift_debug_gauss_table(C.byref(cfg), which, level, f.ctypes.data, C.byref(s), C.byref(sp)))
+    return f, s.value, sp.value
+
+
+def desc_tables(cfg):
+    g = np.zeros((40, 40), np.float32); t = np.zeros(16, np.float32); sc = np.zeros(2, np.float32)
+    _chk(lib().psift_debug_desc_tables(C.byref(cfg), g.ctypes.data, t.ctypes.data, sc.ctypes.data))
+    return g, t, sc
+
+
+def geometry(cfg, w, h):
+    a, b, n = C.c_int(), C.c_int(), C.c_int()
+    _chk(lib().psift_pyramid_geometry(C.byref(cfg), w, h, C.byref(a), C.byref(b), C.byref(n)))
+    return a.value, b.value, n.value

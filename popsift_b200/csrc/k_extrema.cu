@@ -1,0 +1,316 @@
+/* k_extrema.cu -- DoG + 3x3x3 extrema search + sub-pixel refinement, fused, for sm_100a.
+ *
+ * The reference writes five DoG planes per octave (make_dog, s_pyramid_build.cu:74-92) and
+ * scans them with one thread per voxel and point-texture reads (find_extrema_in_dog,
+ * s_extrema.cu:300-562).  Here the DoG is never stored: one thread owns a pixel column
+ * (x,y) of one octave, loads the Gaussian levels it needs once, forms D[l] = G[l+1]-G[l] on
+ * the fly (the same single rounding as make_dog) and tests the `levels` inner DoG levels.
+ * Only voxels that pass the first contrast test look at their 26 neighbours, and only strict
+ * extrema run the Newton refinement, whose neighbour values are re-derived from the
+ * L2-resident Gaussian planes.  One launch covers all octaves.
+ *
+ * The arithmetic of the refinement (gradient, Hessian, closed-form inverse, step rules,
+ * contrast and edge tests) follows s_extrema.cu:122-504 and s_solve.h:24-85 operation by
+ * operation; the fused-multiply-add placement was read off the SASS of the reference build
+ * for sm_100 and is spelled out with intrinsics so that it cannot drift.
+ */
+#include "common.h"
+#include "kernels.h"
+
+namespace psift {
+
+struct DogView {
+    const float* base;
+    size_t       lstride;
+    int          pitch, w, h, nlvl;      /* nlvl = number of Gaussian levels */
+    /* DoG level z at (x,y), clamp-to-edge in x,y and clamp of the layer index like the
+     * reference's layered point texture (sift_octave.cu:231-248, common/assist.h:66-75) */
+    __device__ __forceinline__ float at( int x, int y, int z ) const
+    {
+        x = min( max( x, 0 ), w - 1 );
+        y = min( max( y, 0 ), h - 1 );
+        z = min( max( z, 0 ), nlvl - 2 );
+        const float* p = base + (size_t)z * lstride + (size_t)y * pitch + x;
+        return __fsub_rn( __ldg( p + lstride ), __ldg( p ) );
+    }
+};
+
+/* strict maximum or strict minimum of the 26 neighbours (s_extrema.cu:56-120) */
+__device__ __forceinline__ bool strict_extremum( const DogView& d, int x, int y, int z, float v )
+{
+    bool gt = true, lt = true;
+    #pragma unroll
+    for( int dz = 0; dz < 3; dz++ ) {
+        /* own layer first: most candidates die there */
+        const int zz = z + ( dz == 0 ? 0 : ( dz == 1 ? -1 : 1 ) );
+        #pragma unroll
+        for( int dy = -1; dy <= 1; dy++ )
+            #pragma unroll
+            for( int dx = -1; dx <= 1; dx++ ) {
+                if( dz == 0 && dy == 0 && dx == 0 ) continue;
+                const float f = d.at( x + dx, y + dy, zz );
+                gt = gt && ( v > f );
+                lt = lt && ( v < f );
+            }
+        if( !gt && !lt ) return false;
+    }
+    return gt || lt;
+}
+
+/* closed-form solve of the symmetric 3x3 system (s_solve.h:24-85); A = Dxx, B = Dyy, C = Dss,
+ * a01 = Dxy, a02 = Dxs, a12 = Dys; b is overwritten by the solution.  false: singular. */
+__device__ __forceinline__ bool solve3( float A, float B, float C, float a01, float a02, float a12, float3& b )
+{
+    const float det0 = __fmaf_rn( B,   C,   -__fmul_rn( a12, a12 ) );
+    const float det1 = __fmaf_rn( a12, a02, -__fmul_rn( a01, C   ) );
+    const float det2 = __fmaf_rn( a01, a12, -__fmul_rn( B,   a02 ) );
+    const float det3 = __fmaf_rn( A,   C,   -__fmul_rn( a02, a02 ) );
+    const float det4 = __fmaf_rn( a01, a02, -__fmul_rn( A,   a12 ) );
+    const float det5 = __fmaf_rn( A,   B,   -__fmul_rn( a01, a01 ) );
+    const float det  = __fmaf_rn( a02, det2, __fmaf_rn( A, det0, __fmul_rn( a01, det1 ) ) );
+    if( det == 0.0f ) return false;
+    const float r = __frcp_rn( det );
+    const float i00 = __fmul_rn( det0, r ), i10 = __fmul_rn( det1, r ), i20 = __fmul_rn( det2, r );
+    const float i11 = __fmul_rn( det3, r ), i12 = __fmul_rn( det4, r ), i22 = __fmul_rn( det5, r );
+    const float bx = b.x, by = b.y, bz = b.z;
+    b.x = __fmaf_rn( i20, bz, __fmaf_rn( i10, by, __fmaf_rn( i00, bx, 0.0f ) ) );
+    b.y = __fmaf_rn( i12, bz, __fmaf_rn( i11, by, __fmaf_rn( i10, bx, 0.0f ) ) );
+    b.z = __fmaf_rn( i22, bz, __fmaf_rn( i12, by, __fmaf_rn( i20, bx, 0.0f ) ) );
+    return true;
+}
+
+template<int MODE>
+__device__ __forceinline__ bool first_contrast_ok( float v, float thr )
+{
+    if( MODE == PSIFT_MODE_OPENCV ) return fabsf( v ) >= floorf( thr );                 /* s_extrema.cu:152 */
+    if( MODE == PSIFT_MODE_VLFEAT ) return fabsf( v ) >= __fmul_rn( 0.8f * 2.0f, thr );  /* :203 */
+    return fabsf( v ) >= __fmul_rn( 1.6f, thr );                                         /* :255 */
+}
+
+/* step rule of one Newton iteration: -1 reject, 0 iterate again, 1 converged
+ * (s_extrema.cu:156-190 OpenCV, :207-233 VLFeat, :259-287 PopSift) */
+template<int MODE>
+__device__ __forceinline__ int step_rule( const float3& d, int3& n, int w, int h, int maxlevel, bool last )
+{
+    if( MODE == PSIFT_MODE_OPENCV ) {
+        if( fabsf( d.x ) < 0.5f && fabsf( d.y ) < 0.5f && fabsf( d.z ) < 0.5f ) return 1;
+        n.x = (int)( (float)n.x + roundf( d.x ) );
+        n.y = (int)( (float)n.y + roundf( d.y ) );
+        n.z = (int)( (float)n.z + roundf( d.z ) );
+        return ( n.x < 5 || n.x >= w - 5 || n.y < 5 || n.y >= h - 5 || n.z < 1 || n.z > maxlevel - 2 ) ? -1 : 0;
+    }
+    if( last ) return 0;
+    const int tx = ( ( d.x >= 0.6f && n.x < w - 2 ) ? 1 : 0 ) + ( ( d.x <= -0.6f && n.x > 1 ) ? -1 : 0 );
+    const int ty = ( ( d.y >= 0.6f && n.y < h - 2 ) ? 1 : 0 ) + ( ( d.y <= -0.6f && n.y > 1 ) ? -1 : 0 );
+    int tz = 0;
+    if( MODE == PSIFT_MODE_POPSIFT )   /* VLFeat mode never changes the level, s_extrema.cu:221-229 */
+        tz = ( ( d.z >= 0.6f && n.z < maxlevel - 1 ) ? 1 : 0 ) + ( ( d.z <= -0.6f && n.z > 1 ) ? -1 : 0 );
+    if( tx == 0 && ty == 0 && tz == 0 ) return 1;
+    n.x += tx; n.y += ty; n.z += tz;
+    return 0;
+}
+
+template<int MODE>
+__device__ bool refine_extremum( const DogView& dv, const Consts& k, int x, int y, int level, float val,
+                                 float w_div, float h_div, Cand& out )
+{
+    const int w = dv.w, h = dv.h, maxlevel = dv.nlvl - 1;
+    float3 D, d;
+    float  Dxx, Dyy, Dss, Dxy, Dxs, Dys;
+    int3   n = make_int3( x, y, level );
+    int    iter = 0;
+    d = make_float3( 0.f, 0.f, 0.f );
+    do {
+        iter++;
+        const float x2 = dv.at( n.x + 1, n.y, n.z ), x0 = dv.at( n.x - 1, n.y, n.z );
+        const float y2 = dv.at( n.x, n.y + 1, n.z ), y0 = dv.at( n.x, n.y - 1, n.z );
+        const float z2 = dv.at( n.x, n.y, n.z + 1 ), z0 = dv.at( n.x, n.y, n.z - 1 );
+        const float c  = dv.at( n.x, n.y, n.z );
+        D.x = scalbnf( __fsub_rn( x2, x0 ), -1 );
+        D.y = scalbnf( __fsub_rn( y2, y0 ), -1 );
+        D.z = scalbnf( __fsub_rn( z2, z0 ), -1 );
+        const float c2 = scalbnf( c, 1 );
+        Dxx = __fsub_rn( __fadd_rn( x2, x0 ), c2 );
+        Dyy = __fsub_rn( __fadd_rn( y2, y0 ), c2 );
+        Dss = __fsub_rn( __fadd_rn( z2, z0 ), c2 );
+        /* mixed derivatives: ((++) + (--)) - (-+) - (+-), then /4  (s_extrema.cu:401-403) */
+        Dxy = scalbnf( __fsub_rn( __fsub_rn( __fadd_rn( dv.at( n.x + 1, n.y + 1, n.z ), dv.at( n.x - 1, n.y - 1, n.z ) ),
+                                             dv.at( n.x - 1, n.y + 1, n.z ) ), dv.at( n.x + 1, n.y - 1, n.z ) ), -2 );
+        Dxs = scalbnf( __fsub_rn( __fsub_rn( __fadd_rn( dv.at( n.x + 1, n.y, n.z + 1 ), dv.at( n.x - 1, n.y, n.z - 1 ) ),
+                                             dv.at( n.x - 1, n.y, n.z + 1 ) ), dv.at( n.x + 1, n.y, n.z - 1 ) ), -2 );
+        Dys = scalbnf( __fsub_rn( __fsub_rn( __fadd_rn( dv.at( n.x, n.y + 1, n.z + 1 ), dv.at( n.x, n.y - 1, n.z - 1 ) ),
+                                             dv.at( n.x, n.y + 1, n.z - 1 ) ), dv.at( n.x, n.y - 1, n.z + 1 ) ), -2 );
+        float3 b = make_float3( -D.x, -D.y, -D.z );
+        if( !solve3( Dxx, Dyy, Dss, Dxy, Dxs, Dys, b ) ) {      /* singular: keep the point, zero offset */
+            d = make_float3( 0.f, 0.f, 0.f );
+            break;
+        }
+        d = b;
+        const int rv = step_rule<MODE>( d, n, w, h, maxlevel, iter == 5 );
+        if( rv == -1 ) return false;
+        if( rv == 1 ) break;
+    } while( iter < 5 );
+
+    if( MODE == PSIFT_MODE_OPENCV ) {
+        if( iter >= 5 ) return false;                            /* s_extrema.cu:448-453 */
+    } else {
+        if( d.x >= 1.5f || d.y >= 1.5f || d.z >= 1.5f ) return false;   /* signed on purpose, :455-460 */
+    }
+    const float xn = __fadd_rn( (float)n.x, d.x );
+    const float yn = __fadd_rn( (float)n.y, d.y );
+    const float sn = __fadd_rn( (float)n.z, d.z );
+    if( MODE != PSIFT_MODE_OPENCV ) {                             /* verify(), :235-246 / :289-298 */
+        if( xn < 0.0f || xn > (float)w - 1.0f || yn < 0.0f || yn > (float)h - 1.0f || sn < 0.0f || sn > (float)maxlevel )
+            return false;
+    }
+    const float dot   = __fmaf_rn( D.z, d.z, __fmaf_rn( D.y, d.y, __fmul_rn( D.x, d.x ) ) );
+    const float contr = __fadd_rn( val, scalbnf( dot, -1 ) );
+    const float tr    = __fadd_rn( Dxx, Dyy );
+    const float det   = __fmaf_rn( Dxx, Dyy, -__fmul_rn( Dxy, Dxy ) );
+    const float edge  = __fdiv_rn( __fmul_rn( tr, tr ), det );
+    if( det <= 0.0f ) return false;
+    if( fabsf( contr ) < scalbnf( k.threshold, 1 ) ) return false;
+    const float el1 = __fadd_rn( k.edge_limit, 1.0f );
+    if( edge >= __fdiv_rn( __fmul_rn( el1, el1 ), k.edge_limit ) ) return false;
+
+    out.x     = xn;
+    out.y     = yn;
+    out.lpos  = (int)roundf( sn );
+    out.sigma = __fmul_rn( k.sigma0, powf( k.sigma_k, sn ) );
+    out.cell  = (int)__fadd_rn( __fmul_rn( floorf( __fdiv_rn( yn, h_div ) ), (float)k.grid_size ), floorf( __fdiv_rn( xn, w_div ) ) );
+    return true;
+}
+
+/* block -> (octave, tile) table */
+struct ExtGrid {
+    int first_block[MAX_OCT + 1];
+    int tiles_x[MAX_OCT];
+};
+
+constexpr int EX_TX = 32, EX_TY = 8;
+
+template<int MODE>
+__global__ void __launch_bounds__( EX_TX * EX_TY )
+k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid G, const __grid_constant__ Consts K,
+           Cand* cand, int cand_stride, Counters* ct )
+{
+    int o = 0;
+    while( o + 1 < L.n_oct && (int)blockIdx.x >= G.first_block[o + 1] ) o++;
+    const int tile = blockIdx.x - G.first_block[o];
+    const int w = L.w[o], h = L.h[o];
+    const int x = ( tile % G.tiles_x[o] ) * EX_TX + threadIdx.x + 1;
+    const int y = ( tile / G.tiles_x[o] ) * EX_TY + threadIdx.y + 1;
+
+    DogView dv;
+    dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = L.n_lvl;
+
+    bool inside = ( x <= w - 2 ) && ( y <= h - 2 );
+    if( MODE == PSIFT_MODE_OPENCV ) inside = inside && !( x < 5 || y < 5 || x >= w - 5 || y >= h - 5 );   /* :336-340 */
+
+    const float w_div = __fdiv_rn( (float)w, (float)K.grid_size );
+    const float h_div = __fdiv_rn( (float)h, (float)K.grid_size );
+
+    /* Gaussian column: G[1..nlvl-2] give the inner DoG levels' centre values */
+    float g_prev = 0.f;
+    const float* col = dv.base + (size_t)y * dv.pitch + x;
+    if( inside ) g_prev = __ldg( col + dv.lstride );
+    for( int level = 1; level <= L.n_lvl - 3; level++ ) {
+        bool found = false;
+        Cand c;
+        if( inside ) {
+            const float g_next = __ldg( col + (size_t)( level + 1 ) * dv.lstride );
+            const float val = __fsub_rn( g_next, g_prev );
+            g_prev = g_next;
+            if( first_contrast_ok<MODE>( val, K.threshold ) && strict_extremum( dv, x, y, level, val ) ) {
+                found = refine_extremum<MODE>( dv, K, x, y, level, val, w_div, h_div, c );
+                if( found ) {
+                    c.key_lo = (uint32_t)x | ( (uint32_t)( y & 0xf ) << 28 );
+                    c.key_hi = ( (uint32_t)y >> 4 ) | ( (uint32_t)level << 24 );
+                }
+            }
+        }
+        /* warp-aggregated append (s_extrema.cu:22-44) */
+        const unsigned mask = __ballot_sync( 0xffffffffu, found );
+        if( mask ) {
+            const int lane = threadIdx.x & 31;
+            int base = 0;
+            if( lane == 0 ) base = atomicAdd( &ct->ext_ct[o], __popc( mask ) );
+            base = __shfl_sync( 0xffffffffu, base, 0 );
+            const int idx = base + __popc( mask & ( ( 1u << lane ) - 1 ) );
+            if( found && idx < K.max_extrema ) cand[(size_t)o * cand_stride + idx] = c;
+        }
+    }
+}
+
+/* Clamp the per-octave counters to max_extrema (s_extrema.cu:555-561), build the prefix sums,
+ * and flag overflow.  One thread. */
+__global__ void k_extrema_finish( Counters* ct, int n_oct, int max_extrema, int ext_capacity )
+{
+    if( threadIdx.x != 0 || blockIdx.x != 0 ) return;
+    int ps = 0;
+    for( int o = 0; o < MAX_OCT; o++ ) {
+        int c = ( o < n_oct ) ? min( ct->ext_ct[o], max_extrema ) : 0;
+        if( ps + c > ext_capacity ) { c = max( 0, ext_capacity - ps ); ct->overflow = 1; }
+        ct->ext_ct[o] = c;
+        ct->ext_ps[o] = ps;
+        ps += c;
+    }
+    ct->ext_ps[MAX_OCT] = ps;
+    ct->ext_total = ps;
+}
+
+/* Deterministic order: rank every candidate of an octave by its detection voxel
+ * (level, y, x) and scatter it to ext_ps[o] + rank.  The reference's order is whatever its
+ * atomics produced (its own regression test sorts the output, testOxfordDataset.sh.in:138-155).
+ * Keys are unique, so this is a permutation.  O(n^2/P) but n is a few thousand per octave. */
+constexpr int RS_NT = 256;
+__global__ void __launch_bounds__( RS_NT )
+k_rank_sort( const Cand* cand, int cand_stride, const Counters* ct, int n_oct, Cand* sorted )
+{
+    __shared__ unsigned long long keys[RS_NT];
+    const int o = blockIdx.y;
+    const int n = ct->ext_ct[o];
+    const Cand* src = cand + (size_t)o * cand_stride;
+    for( int i0 = blockIdx.x * RS_NT; i0 < n; i0 += gridDim.x * RS_NT ) {
+        const int i = i0 + threadIdx.x;
+        unsigned long long mykey = 0;
+        if( i < n ) mykey = ( (unsigned long long)src[i].key_hi << 32 ) | src[i].key_lo;
+        int rank = 0;
+        for( int j0 = 0; j0 < n; j0 += RS_NT ) {
+            __syncthreads();
+            const int j = j0 + threadIdx.x;
+            keys[threadIdx.x] = ( j < n ) ? ( ( (unsigned long long)src[j].key_hi << 32 ) | src[j].key_lo ) : ~0ull;
+            __syncthreads();
+            const int m = min( RS_NT, n - j0 );
+            for( int q = 0; q < m; q++ ) rank += ( keys[q] < mykey ) ? 1 : 0;
+        }
+        if( i < n ) sorted[ct->ext_ps[o] + rank] = src[i];
+    }
+}
+
+cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted,
+                            int ext_capacity, Counters* ct, cudaStream_t st, long long* launches )
+{
+    ExtGrid G;
+    int nb = 0;
+    for( int o = 0; o < L.n_oct; o++ ) {
+        G.first_block[o] = nb;
+        const int tx = ( max( L.w[o] - 2, 1 ) + EX_TX - 1 ) / EX_TX;
+        const int ty = ( max( L.h[o] - 2, 1 ) + EX_TY - 1 ) / EX_TY;
+        G.tiles_x[o] = tx;
+        nb += tx * ty;
+    }
+    for( int o = L.n_oct; o <= MAX_OCT; o++ ) G.first_block[o] = nb;
+    dim3 block( EX_TX, EX_TY );
+    switch( K.sift_mode ) {
+    case PSIFT_MODE_OPENCV: k_extrema<PSIFT_MODE_OPENCV><<<nb, block, 0, st>>>( L, G, K, cand, cand_stride, ct ); break;
+    case PSIFT_MODE_VLFEAT: k_extrema<PSIFT_MODE_VLFEAT><<<nb, block, 0, st>>>( L, G, K, cand, cand_stride, ct ); break;
+    default:                k_extrema<PSIFT_MODE_POPSIFT><<<nb, block, 0, st>>>( L, G, K, cand, cand_stride, ct ); break;
+    }
+    k_extrema_finish<<<1, 32, 0, st>>>( ct, L.n_oct, K.max_extrema, ext_capacity );
+    k_rank_sort<<<dim3( 8, L.n_oct ), RS_NT, 0, st>>>( cand, cand_stride, ct, L.n_oct, sorted );
+    if( launches ) *launches += 3;
+    return cudaGetLastError();
+}
+
+} // namespace psift

@@ -1,0 +1,578 @@
+/* pipeline.cu -- per-device context, frame slots, launch sequence and the C ABI (include/psift.h).
+ *
+ * Replaces the reference's Pyramid/Octave/Image host objects (sift_pyramid.cu:108-239,
+ * sift_octave.cu:33-89, s_image.cu:64-169) and its process-global device symbols
+ * (sift_pyramid.cu:38-49) by a context that owns everything it touches, so several
+ * contexts (one per GPU, or several per GPU) can live in one process.
+ *
+ * A frame runs entirely stream-ordered on its slot's stream: upload -> pyramid ->
+ * DoG/extrema -> order -> orientation -> prefix -> descriptors(+norm) -> features ->
+ * counter download.  Later stages read their work counts on the device, so the host
+ * never has to wait in the middle of a frame (the reference synchronises the device
+ * at least five times per image, see s_orientation.cu:351,427; sift_desc.cu:61,109).
+ * psift_wait() then copies exactly n_feat features and n_desc descriptors.
+ */
+#include "common.h"
+#include "kernels.h"
+#include <cstdio>
+#include <cstring>
+#include <cstdarg>
+#include <vector>
+#include <mutex>
+#include <new>
+
+using namespace psift;
+
+static thread_local char g_err[512] = "";
+static int fail( int code, const char* fmt, ... )
+{
+    va_list ap; va_start( ap, fmt ); vsnprintf( g_err, sizeof g_err, fmt, ap ); va_end( ap );
+    return code;
+}
+#define CU( call ) do { cudaError_t e_ = ( call ); if( e_ != cudaSuccess ) \
+    return fail( PSIFT_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString( e_ ), __FILE__, __LINE__ ); } while( 0 )
+
+namespace {
+
+constexpr int N_EVENTS = 7;
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t  ev[N_EVENTS] = {};
+    cudaEvent_t  ev_counters = nullptr;
+    bool         busy = false;
+
+    /* input */
+    void*  d_img = nullptr; size_t img_pitch = 0; int img_w = 0, img_h = 0, img_elem = 0; size_t img_cap_w = 0, img_cap_h = 0;
+    cudaTextureObject_t img_tex = 0;
+    const void* tex_bound_ptr = nullptr; size_t tex_bound_pitch = 0;
+    void*  h_img = nullptr; size_t h_img_cap = 0;          /* pinned private copy of the caller's image */
+
+    /* pyramid */
+    float* arena = nullptr; size_t arena_floats = 0;
+    PyrLayout L;
+    int in_w = 0, in_h = 0;
+    std::vector<cudaTextureObject_t> lintex_h;
+    cudaTextureObject_t* lintex_d = nullptr;
+
+    /* keypoints */
+    Cand* cand = nullptr; Cand* sorted = nullptr;
+    int cand_stride = 0, ext_cap = 0, desc_cap = 0;
+    psift_extremum* ext = nullptr;
+    psift_feature*  feat = nullptr;
+    int*   desc_map = nullptr;
+    float* desc = nullptr;
+    Counters* ct = nullptr;
+
+    /* host results (pinned) */
+    Counters* h_ct = nullptr;
+    psift_extremum* h_ext = nullptr; psift_feature* h_feat = nullptr; float* h_desc = nullptr;
+    int h_ext_cap = 0, h_desc_cap = 0;
+};
+
+} // namespace
+
+struct psift_ctx {
+    int device = 0;
+    psift_config cfg;
+    GaussTables  gt;
+    Consts       K;
+    DescTables   dt;
+    DescTables*  d_dt = nullptr;
+    std::vector<Slot> slots;
+    int next_slot = 0;
+    long long launches = 0;
+    float last_ms[8] = { 0 };
+    int last_slot = -1;
+    std::mutex mu;
+};
+
+struct psift_job {
+    psift_ctx* ctx;
+    int slot;
+    bool waited;
+    int status;
+};
+
+static bool linear_needed( int desc_mode ) { return desc_mode == PSIFT_DESC_IGRID || desc_mode == PSIFT_DESC_NOTILE || desc_mode == PSIFT_DESC_ILOOP; }
+
+static void free_slot_pyramid( Slot& s )
+{
+    for( auto t : s.lintex_h ) if( t ) cudaDestroyTextureObject( t );
+    s.lintex_h.clear();
+    if( s.lintex_d ) { cudaFree( s.lintex_d ); s.lintex_d = nullptr; }
+    if( s.arena ) { cudaFree( s.arena ); s.arena = nullptr; s.arena_floats = 0; }
+    s.in_w = s.in_h = 0;
+}
+
+static void free_slot( Slot& s )
+{
+    free_slot_pyramid( s );
+    if( s.img_tex ) cudaDestroyTextureObject( s.img_tex );
+    if( s.d_img ) cudaFree( s.d_img );
+    if( s.h_img ) cudaFreeHost( s.h_img );
+    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.ct );
+    if( s.h_ct ) cudaFreeHost( s.h_ct );
+    if( s.h_ext ) cudaFreeHost( s.h_ext );
+    if( s.h_feat ) cudaFreeHost( s.h_feat );
+    if( s.h_desc ) cudaFreeHost( s.h_desc );
+    for( auto& e : s.ev ) if( e ) cudaEventDestroy( e );
+    if( s.ev_counters ) cudaEventDestroy( s.ev_counters );
+    if( s.stream ) cudaStreamDestroy( s.stream );
+    s = Slot();
+}
+
+/* (re)build the pyramid geometry of a slot for an input size (Pyramid::Pyramid / resetDimensions,
+ * sift_pyramid.cu:108-177; octave sizes by repeated ceil(/2), :132-134) */
+static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h )
+{
+    if( s.in_w == w && s.in_h == h && s.arena ) return PSIFT_OK;
+    int w0, h0;
+    octave0_size( c->cfg, w, h, w0, h0 );
+    const int n_oct = octave_count( c->cfg, w, h );
+    const int n_lvl = c->cfg.levels + 3;
+    PyrLayout L;
+    memset( &L, 0, sizeof L );
+    L.n_oct = n_oct; L.n_lvl = n_lvl;
+    size_t total = 0;
+    int ow = w0, oh = h0;
+    std::vector<size_t> off( n_oct );
+    for( int o = 0; o < n_oct; o++ ) {
+        if( ow < 1 || oh < 1 ) return fail( PSIFT_E_INVALID, "image %dx%d too small for %d octaves", w, h, n_oct );
+        L.w[o] = ow; L.h[o] = oh;
+        L.pitch[o] = ( ow + 31 ) / 32 * 32;
+        L.lstride[o] = ( (size_t)L.pitch[o] * oh + 127 ) / 128 * 128;      /* keep planes 512-byte aligned (textures) */
+        off[o] = total;
+        total += L.lstride[o] * n_lvl;
+        ow = (int)ceilf( ow / 2.0f );
+        oh = (int)ceilf( oh / 2.0f );
+    }
+    if( total > s.arena_floats ) {
+        free_slot_pyramid( s );
+        CU( cudaMalloc( &s.arena, total * sizeof(float) ) );
+        s.arena_floats = total;
+    } else {
+        for( auto t : s.lintex_h ) if( t ) cudaDestroyTextureObject( t );
+        s.lintex_h.clear();
+    }
+    for( int o = 0; o < n_oct; o++ ) L.base[o] = s.arena + off[o];
+    s.L = L; s.in_w = w; s.in_h = h;
+
+    if( linear_needed( c->cfg.desc_mode ) ) {
+        /* bilinear point-of-view of every Gaussian level (Octave::alloc_data_tex, sift_octave.cu:211-248) */
+        s.lintex_h.assign( (size_t)n_oct * n_lvl, 0 );
+        for( int o = 0; o < n_oct; o++ )
+            for( int l = 0; l < n_lvl; l++ ) {
+                cudaResourceDesc rd; memset( &rd, 0, sizeof rd );
+                rd.resType = cudaResourceTypePitch2D;
+                rd.res.pitch2D.devPtr = L.base[o] + (size_t)l * L.lstride[o];
+                rd.res.pitch2D.desc = cudaCreateChannelDesc( 32, 0, 0, 0, cudaChannelFormatKindFloat );
+                rd.res.pitch2D.width = L.w[o]; rd.res.pitch2D.height = L.h[o];
+                rd.res.pitch2D.pitchInBytes = (size_t)L.pitch[o] * sizeof(float);
+                cudaTextureDesc td; memset( &td, 0, sizeof td );
+                td.normalizedCoords = 0;
+                td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+                td.readMode = cudaReadModeElementType;
+                td.filterMode = cudaFilterModeLinear;
+                CU( cudaCreateTextureObject( &s.lintex_h[(size_t)o * n_lvl + l], &rd, &td, nullptr ) );
+            }
+        if( s.lintex_d ) cudaFree( s.lintex_d );
+        CU( cudaMalloc( &s.lintex_d, s.lintex_h.size() * sizeof(cudaTextureObject_t) ) );
+        CU( cudaMemcpy( s.lintex_d, s.lintex_h.data(), s.lintex_h.size() * sizeof(cudaTextureObject_t), cudaMemcpyHostToDevice ) );
+    }
+    return PSIFT_OK;
+}
+
+static int bind_input_texture( Slot& s, const void* dptr, size_t pitch, int w, int h, int elem )
+{
+    if( s.img_tex && s.tex_bound_ptr == dptr && s.tex_bound_pitch == pitch && s.img_w == w && s.img_h == h && s.img_elem == elem ) return PSIFT_OK;
+    if( s.img_tex ) { cudaDestroyTextureObject( s.img_tex ); s.img_tex = 0; }
+    /* Image::createTexture / ImageFloat::createTexture, s_image.cu:140-169, 264-293 */
+    cudaResourceDesc rd; memset( &rd, 0, sizeof rd );
+    rd.resType = cudaResourceTypePitch2D;
+    rd.res.pitch2D.devPtr = const_cast<void*>( dptr );
+    rd.res.pitch2D.desc = ( elem == 1 ) ? cudaCreateChannelDesc( 8, 0, 0, 0, cudaChannelFormatKindUnsigned )
+                                        : cudaCreateChannelDesc( 32, 0, 0, 0, cudaChannelFormatKindFloat );
+    rd.res.pitch2D.pitchInBytes = pitch; rd.res.pitch2D.width = w; rd.res.pitch2D.height = h;
+    cudaTextureDesc td; memset( &td, 0, sizeof td );
+    td.normalizedCoords = 1;
+    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+    td.readMode = ( elem == 1 ) ? cudaReadModeNormalizedFloat : cudaReadModeElementType;
+    td.filterMode = cudaFilterModeLinear;
+    CU( cudaCreateTextureObject( &s.img_tex, &rd, &td, nullptr ) );
+    s.tex_bound_ptr = dptr; s.tex_bound_pitch = pitch; s.img_w = w; s.img_h = h; s.img_elem = elem;
+    return PSIFT_OK;
+}
+
+static int init_slot( psift_ctx* c, Slot& s )
+{
+    CU( cudaStreamCreateWithFlags( &s.stream, cudaStreamNonBlocking ) );
+    for( auto& e : s.ev ) CU( cudaEventCreate( &e ) );
+    CU( cudaEventCreateWithFlags( &s.ev_counters, cudaEventDisableTiming ) );
+    const int me = c->cfg.max_extrema;
+    s.cand_stride = me;
+    s.ext_cap  = me;                                     /* sift_pyramid.cu:148-151 */
+    s.desc_cap = std::max( 2 * me, me + me / 4 );          /* sift_pyramid.cu:153-159 */
+    CU( cudaMalloc( &s.cand,   sizeof(Cand) * (size_t)me * MAX_OCT ) );
+    CU( cudaMalloc( &s.sorted, sizeof(Cand) * (size_t)s.ext_cap ) );
+    CU( cudaMalloc( &s.ext,    sizeof(psift_extremum) * (size_t)s.ext_cap ) );
+    CU( cudaMalloc( &s.feat,   sizeof(psift_feature) * (size_t)s.ext_cap ) );
+    CU( cudaMalloc( &s.desc_map, sizeof(int) * (size_t)s.desc_cap ) );
+    CU( cudaMalloc( &s.desc,   sizeof(float) * 128 * (size_t)s.desc_cap ) );
+    CU( cudaMalloc( &s.ct, sizeof(Counters) ) );
+    CU( cudaMallocHost( &s.h_ct, sizeof(Counters) ) );
+    return PSIFT_OK;
+}
+
+static int ensure_host_results( Slot& s, int n_ext, int n_desc )
+{
+    if( n_ext > s.h_ext_cap ) {
+        if( s.h_ext ) cudaFreeHost( s.h_ext );
+        if( s.h_feat ) cudaFreeHost( s.h_feat );
+        const int cap = std::max( 4096, n_ext + n_ext / 2 );
+        CU( cudaMallocHost( &s.h_ext, sizeof(psift_extremum) * (size_t)cap ) );
+        CU( cudaMallocHost( &s.h_feat, sizeof(psift_feature) * (size_t)cap ) );
+        s.h_ext_cap = cap;
+    }
+    if( n_desc > s.h_desc_cap ) {
+        if( s.h_desc ) cudaFreeHost( s.h_desc );
+        const int cap = std::max( 8192, n_desc + n_desc / 2 );
+        CU( cudaMallocHost( &s.h_desc, sizeof(float) * 128 * (size_t)cap ) );
+        s.h_desc_cap = cap;
+    }
+    return PSIFT_OK;
+}
+
+/* queue one frame on the slot's stream; the input texture is already bound */
+static int run_frame( psift_ctx* c, Slot& s )
+{
+    cudaStream_t st = s.stream;
+    const PyrLayout& L = s.L;
+    CU( cudaEventRecord( s.ev[1], st ) );
+    CU( cudaMemsetAsync( s.ct, 0, sizeof(Counters), st ) );           /* reset_extrema_mgmt, sift_pyramid.cu:363-370 */
+    float shift = 0.5f;                                              /* s_pyramid_build.cu:110-114 */
+    if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT )
+        shift = 0.5f * powf( 2.0f, c->cfg.upscale_factor );
+    CU( launch_pyramid( L, s.img_tex, shift, c->gt, st, &c->launches ) );
+    CU( cudaEventRecord( s.ev[2], st ) );
+    CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
+    CU( cudaEventRecord( s.ev[3], st ) );
+    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, 148 * 2, st, &c->launches ) );
+    CU( cudaEventRecord( s.ev[4], st ) );
+    CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.lintex_d, c->d_dt, s.desc, s.feat, 148 * 4, st, &c->launches ) );
+    CU( cudaEventRecord( s.ev[5], st ) );
+    CU( cudaMemcpyAsync( s.h_ct, s.ct, sizeof(Counters), cudaMemcpyDeviceToHost, st ) );
+    CU( cudaEventRecord( s.ev_counters, st ) );
+    return PSIFT_OK;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/*                                           C ABI                                            */
+/* ------------------------------------------------------------------------------------------ */
+
+namespace psift {
+__global__ void k_dog_plane( const float* lo, const float* hi, float* out, int w, int h, int pitch )
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if( x < w && y < h ) out[(size_t)y * w + x] = __fsub_rn( hi[(size_t)y * pitch + x], lo[(size_t)y * pitch + x] );
+}
+cudaError_t launch_dog_plane( const float* lo, const float* hi, float* out, int w, int h, int pitch, cudaStream_t st )
+{
+    k_dog_plane<<<dim3( ( w + 127 ) / 128, h ), 128, 0, st>>>( lo, hi, out, w, h, pitch );
+    return cudaGetLastError();
+}
+}
+
+extern "C" {
+
+const char* psift_last_error( void ) { return g_err; }
+
+void psift_config_default( psift_config* c )
+{
+    /* popsift::Config::Config(), sift_conf.cu:17-40 */
+    c->octaves = -1; c->levels = 3; c->sigma = 1.6f; c->edge_limit = 10.0f; c->threshold = 0.04f;
+    c->upscale_factor = 1.0f;
+    c->gauss_mode = PSIFT_GAUSS_VLFEAT_COMPUTE; c->sift_mode = PSIFT_MODE_POPSIFT;
+    c->desc_mode = PSIFT_DESC_LOOP; c->norm_mode = PSIFT_NORM_ROOTSIFT; c->norm_multi = 0;
+    c->max_extrema = 100000; c->filter_max_extrema = -1; c->filter_grid_size = 2;
+    c->filter_sorting = PSIFT_FILTER_RANDOM;
+    c->assume_initial_blur = 1; c->initial_blur = 0.5f;
+    c->deterministic_order = 1;
+}
+
+int psift_device_count( void )
+{
+    int n = 0;
+    if( cudaGetDeviceCount( &n ) != cudaSuccess ) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+static int check_config( const psift_config* cfg )
+{
+    if( !cfg ) return fail( PSIFT_E_INVALID, "null config" );
+    if( cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_COMPUTE && cfg->gauss_mode != PSIFT_GAUSS_OPENCV_COMPUTE )
+        return fail( PSIFT_E_INVALID, "gauss mode %d not built yet (vlfeat and opencv are)", cfg->gauss_mode );
+    if( cfg->desc_mode == PSIFT_DESC_ILOOP ) return fail( PSIFT_E_INVALID, "desc mode iloop not built yet" );
+    if( cfg->desc_mode < 0 || cfg->desc_mode > PSIFT_DESC_NOTILE ) return fail( PSIFT_E_INVALID, "bad desc mode" );
+    if( cfg->sift_mode < 0 || cfg->sift_mode > PSIFT_MODE_VLFEAT ) return fail( PSIFT_E_INVALID, "bad sift mode" );
+    if( cfg->max_extrema < 1 ) return fail( PSIFT_E_INVALID, "max_extrema must be positive" );
+    if( cfg->upscale_factor != floorf( cfg->upscale_factor ) || cfg->upscale_factor > 4 || cfg->upscale_factor < -8 )
+        return fail( PSIFT_E_INVALID, "downsampling must be an integer in [-4, 8]" );
+    if( cfg->filter_grid_size < 1 ) return fail( PSIFT_E_INVALID, "filter grid size must be positive" );
+    return PSIFT_OK;
+}
+
+int psift_debug_gauss_table( const psift_config* cfg_in, int which, int level, float* filter32, float* sigma, int* span )
+{
+    if( !cfg_in ) return fail( PSIFT_E_INVALID, "null config" );
+    psift_config cfg = *cfg_in;
+    cfg.levels = std::max( 2, cfg.levels );                      /* popsift.cpp:71 */
+    GaussTables gt; const char* err = "";
+    if( !build_gauss_tables( cfg, gt, &err ) ) return fail( PSIFT_E_INVALID, "%s", err );
+    const Taps* t = nullptr; float sg = 0.f;
+    const int lim = ( which == 3 ) ? MAX_OCT : MAX_LVL;
+    if( level < 0 || level >= lim ) return fail( PSIFT_E_INVALID, "level out of range" );
+    switch( which ) {
+    case 0: t = &gt.inc[level];    sg = gt.inc_sigma[level]; break;
+    case 1: t = &gt.abs_o0[level]; sg = gt.abs_o0_sigma[level]; break;
+    case 2: t = &gt.abs_oN[level]; sg = gt.abs_oN_sigma[level]; break;
+    case 3: t = &gt.dd[level];     sg = gt.dd_sigma[level]; break;
+    default: return fail( PSIFT_E_INVALID, "which must be 0..3" );
+    }
+    if( filter32 ) memcpy( filter32, t->g, sizeof(float) * TAP_ALIGN );
+    if( sigma ) *sigma = sg;
+    if( span ) *span = t->span;
+    return PSIFT_OK;
+}
+
+int psift_debug_desc_tables( const psift_config* cfg_in, float* desc_gauss_1600, float* desc_tile_16, float* scalars2 )
+{
+    if( !cfg_in ) return fail( PSIFT_E_INVALID, "null config" );
+    psift_config cfg = *cfg_in;
+    cfg.levels = std::max( 2, cfg.levels );
+    Consts K; DescTables* dt = new DescTables;
+    build_consts( cfg, K, *dt );
+    if( desc_gauss_1600 ) memcpy( desc_gauss_1600, dt->desc_gauss, sizeof dt->desc_gauss );
+    if( desc_tile_16 ) memcpy( desc_tile_16, dt->desc_tile, sizeof dt->desc_tile );
+    if( scalars2 ) { scalars2[0] = K.sigma_k; scalars2[1] = K.threshold; }
+    delete dt;
+    return PSIFT_OK;
+}
+
+int psift_pyramid_geometry( const psift_config* cfg, int w, int h, int* w0, int* h0, int* n_octaves )
+{
+    if( !cfg || w < 1 || h < 1 ) return fail( PSIFT_E_INVALID, "bad arguments" );
+    int a, b; octave0_size( *cfg, w, h, a, b );
+    if( w0 ) *w0 = a;
+    if( h0 ) *h0 = b;
+    if( n_octaves ) *n_octaves = octave_count( *cfg, w, h );
+    return PSIFT_OK;
+}
+
+int psift_configure( psift_ctx* c, const psift_config* cfg_in )
+{
+    if( !c ) return fail( PSIFT_E_INVALID, "null context" );
+    int rc = check_config( cfg_in );
+    if( rc ) return rc;
+    std::lock_guard<std::mutex> lk( c->mu );
+    for( auto& s : c->slots ) if( s.busy ) return fail( PSIFT_E_STATE, "configure while jobs are in flight" );
+    psift_config cfg = *cfg_in;
+    cfg.levels = std::max( 2, cfg.levels );                      /* popsift.cpp:71 */
+    GaussTables gt; const char* err = "";
+    if( !build_gauss_tables( cfg, gt, &err ) ) return fail( PSIFT_E_INVALID, "%s", err );
+    CU( cudaSetDevice( c->device ) );
+    const bool realloc_slots = c->slots.empty() || cfg.max_extrema != c->cfg.max_extrema;
+    c->cfg = cfg; c->gt = gt;
+    build_consts( cfg, c->K, c->dt );
+    if( !c->d_dt ) CU( cudaMalloc( &c->d_dt, sizeof(DescTables) ) );
+    CU( cudaMemcpy( c->d_dt, &c->dt, sizeof(DescTables), cudaMemcpyHostToDevice ) );
+    if( realloc_slots ) {
+        for( auto& s : c->slots ) free_slot( s );
+        c->slots.assign( 4, Slot() );
+        for( auto& s : c->slots ) { rc = init_slot( c, s ); if( rc ) return rc; }
+    } else {
+        for( auto& s : c->slots ) free_slot_pyramid( s );      /* geometry may change with the config */
+    }
+    return PSIFT_OK;
+}
+
+int psift_create( int device, const psift_config* cfg, psift_ctx** out )
+{
+    if( !out ) return fail( PSIFT_E_INVALID, "null out pointer" );
+    *out = nullptr;
+    int n = psift_device_count();
+    if( n <= 0 ) return fail( PSIFT_E_NODEVICE, "no CUDA device: this library has no CPU path" );
+    if( device < 0 || device >= n ) return fail( PSIFT_E_INVALID, "device %d out of range (0..%d)", device, n - 1 );
+    psift_config def;
+    if( !cfg ) { psift_config_default( &def ); cfg = &def; }
+    psift_ctx* c = new( std::nothrow ) psift_ctx;
+    if( !c ) return fail( PSIFT_E_INVALID, "out of memory" );
+    c->device = device;
+    int rc = psift_configure( c, cfg );
+    if( rc ) { psift_destroy( c ); return rc; }
+    *out = c;
+    return PSIFT_OK;
+}
+
+void psift_destroy( psift_ctx* c )
+{
+    if( !c ) return;
+    cudaSetDevice( c->device );
+    for( auto& s : c->slots ) { if( s.stream ) cudaStreamSynchronize( s.stream ); free_slot( s ); }
+    if( c->d_dt ) cudaFree( c->d_dt );
+    delete c;
+}
+
+static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pitch, int elem, bool on_device, psift_job** out )
+{
+    if( !c || !out || !src ) return fail( PSIFT_E_INVALID, "null argument" );
+    *out = nullptr;
+    if( w < 1 || h < 1 ) return fail( PSIFT_E_INVALID, "bad image size %dx%d", w, h );
+    if( pitch == 0 ) pitch = (size_t)w * elem;
+    if( pitch < (size_t)w * elem ) return fail( PSIFT_E_INVALID, "pitch smaller than a row" );
+    std::lock_guard<std::mutex> lk( c->mu );
+    CU( cudaSetDevice( c->device ) );
+    int si = -1;
+    for( size_t k = 0; k < c->slots.size(); k++ ) {
+        const int cand = ( c->next_slot + (int)k ) % (int)c->slots.size();
+        if( !c->slots[cand].busy ) { si = cand; break; }
+    }
+    if( si < 0 ) return fail( PSIFT_E_STATE, "all %d frame slots are in flight: wait for and free a job first", (int)c->slots.size() );
+    c->next_slot = ( si + 1 ) % (int)c->slots.size();
+    Slot& s = c->slots[si];
+    int rc = setup_pyramid( c, s, w, h );
+    if( rc ) return rc;
+    CU( cudaEventRecord( s.ev[0], s.stream ) );
+    if( on_device ) {
+        if( pitch % 32 || ( (uintptr_t)src % 512 ) )
+            return fail( PSIFT_E_INVALID, "device image needs a 512-byte aligned base and a pitch that is a multiple of 32" );
+        rc = bind_input_texture( s, src, pitch, w, h, elem );
+        if( rc ) return rc;
+    } else {
+        /* private pinned copy (SiftJob::SiftJob, popsift.cpp:238-253; Image::load, s_image.cu:71-79) */
+        const size_t row = (size_t)w * elem, need = row * h;
+        if( need > s.h_img_cap ) {
+            if( s.h_img ) cudaFreeHost( s.h_img );
+            CU( cudaMallocHost( &s.h_img, need ) );
+            s.h_img_cap = need;
+        }
+        for( int y = 0; y < h; y++ ) memcpy( (char*)s.h_img + y * row, (const char*)src + y * pitch, row );
+        if( !s.d_img || s.img_cap_w < row || s.img_cap_h < (size_t)h ) {
+            if( s.img_tex ) { cudaDestroyTextureObject( s.img_tex ); s.img_tex = 0; }
+            if( s.d_img ) cudaFree( s.d_img );
+            s.img_cap_w = std::max( s.img_cap_w, row ); s.img_cap_h = std::max( s.img_cap_h, (size_t)h );
+            CU( cudaMallocPitch( &s.d_img, &s.img_pitch, s.img_cap_w, s.img_cap_h ) );
+        }
+        CU( cudaMemcpy2DAsync( s.d_img, s.img_pitch, s.h_img, row, row, h, cudaMemcpyHostToDevice, s.stream ) );
+        rc = bind_input_texture( s, s.d_img, s.img_pitch, w, h, elem );
+        if( rc ) return rc;
+    }
+    rc = run_frame( c, s );
+    if( rc ) return rc;
+    s.busy = true;
+    psift_job* j = new psift_job;
+    j->ctx = c; j->slot = si; j->waited = false; j->status = PSIFT_OK;
+    *out = j;
+    return PSIFT_OK;
+}
+
+int psift_submit_u8( psift_ctx* c, int w, int h, const uint8_t* host, size_t pitch, psift_job** out )
+{ return submit_common( c, w, h, host, pitch, 1, false, out ); }
+int psift_submit_f32( psift_ctx* c, int w, int h, const float* host, size_t pitch, psift_job** out )
+{ return submit_common( c, w, h, host, pitch, 4, false, out ); }
+int psift_submit_dev_u8( psift_ctx* c, int w, int h, const uint8_t* dev, size_t pitch, psift_job** out )
+{ return submit_common( c, w, h, dev, pitch, 1, true, out ); }
+
+int psift_wait( psift_job* j, psift_result* r )
+{
+    if( !j || !r ) return fail( PSIFT_E_INVALID, "null argument" );
+    psift_ctx* c = j->ctx;
+    Slot& s = c->slots[j->slot];
+    CU( cudaSetDevice( c->device ) );
+    if( !j->waited ) {
+        CU( cudaEventSynchronize( s.ev_counters ) );
+        const int n_ext = s.h_ct->ext_total, n_desc = s.h_ct->ori_total;
+        int rc = ensure_host_results( s, n_ext, n_desc );
+        if( rc ) return rc;
+        if( n_ext > 0 ) {
+            CU( cudaMemcpyAsync( s.h_feat, s.feat, sizeof(psift_feature) * (size_t)n_ext, cudaMemcpyDeviceToHost, s.stream ) );
+            CU( cudaMemcpyAsync( s.h_ext,  s.ext,  sizeof(psift_extremum) * (size_t)n_ext, cudaMemcpyDeviceToHost, s.stream ) );
+        }
+        if( n_desc > 0 )
+            CU( cudaMemcpyAsync( s.h_desc, s.desc, sizeof(float) * 128 * (size_t)n_desc, cudaMemcpyDeviceToHost, s.stream ) );
+        CU( cudaEventRecord( s.ev[6], s.stream ) );
+        CU( cudaStreamSynchronize( s.stream ) );
+        j->waited = true;
+        std::lock_guard<std::mutex> lk( c->mu );
+        float ms = 0.f;
+        for( int k = 0; k < 6; k++ ) { if( cudaEventElapsedTime( &ms, s.ev[k], s.ev[k + 1] ) == cudaSuccess ) c->last_ms[k] = ms; }
+        if( cudaEventElapsedTime( &ms, s.ev[0], s.ev[6] ) == cudaSuccess ) c->last_ms[6] = ms;
+        c->last_slot = j->slot;
+    }
+    memset( r, 0, sizeof *r );
+    r->n_feat = s.h_ct->ext_total; r->n_desc = s.h_ct->ori_total;
+    r->feat = s.h_feat; r->desc = s.h_desc; r->ext = s.h_ext;
+    for( int o = 0; o < MAX_OCT; o++ ) { r->ext_ct[o] = s.h_ct->ext_ct[o]; r->ori_ct[o] = s.h_ct->ori_ct[o]; }
+    r->n_octaves = s.L.n_oct; r->n_levels = s.L.n_lvl; r->w0 = s.L.w[0]; r->h0 = s.L.h[0];
+    return PSIFT_OK;
+}
+
+void psift_job_free( psift_job* j )
+{
+    if( !j ) return;
+    psift_ctx* c = j->ctx;
+    Slot& s = c->slots[j->slot];
+    if( !j->waited ) { cudaSetDevice( c->device ); cudaStreamSynchronize( s.stream ); }
+    { std::lock_guard<std::mutex> lk( c->mu ); s.busy = false; }
+    delete j;
+}
+
+int psift_octave_size( psift_ctx* c, int octave, int* w, int* h )
+{
+    if( !c || c->last_slot < 0 ) return fail( PSIFT_E_STATE, "no finished job" );
+    const Slot& s = c->slots[c->last_slot];
+    if( octave < 0 || octave >= s.L.n_oct ) return fail( PSIFT_E_INVALID, "octave out of range" );
+    if( w ) *w = s.L.w[octave];
+    if( h ) *h = s.L.h[octave];
+    return PSIFT_OK;
+}
+
+int psift_debug_read_level( psift_ctx* c, int octave, int level, float* out )
+{
+    if( !c || c->last_slot < 0 || !out ) return fail( PSIFT_E_STATE, "no finished job" );
+    const Slot& s = c->slots[c->last_slot];
+    if( octave < 0 || octave >= s.L.n_oct || level < 0 || level >= s.L.n_lvl ) return fail( PSIFT_E_INVALID, "octave/level out of range" );
+    CU( cudaSetDevice( c->device ) );
+    const float* p = s.L.base[octave] + (size_t)level * s.L.lstride[octave];
+    CU( cudaMemcpy2D( out, (size_t)s.L.w[octave] * 4, p, (size_t)s.L.pitch[octave] * 4, (size_t)s.L.w[octave] * 4, s.L.h[octave], cudaMemcpyDeviceToHost ) );
+    return PSIFT_OK;
+}
+
+int psift_debug_read_dog( psift_ctx* c, int octave, int level, float* out )
+{
+    if( !c || c->last_slot < 0 || !out ) return fail( PSIFT_E_STATE, "no finished job" );
+    const Slot& s = c->slots[c->last_slot];
+    if( octave < 0 || octave >= s.L.n_oct || level < 0 || level >= s.L.n_lvl - 1 ) return fail( PSIFT_E_INVALID, "octave/level out of range" );
+    CU( cudaSetDevice( c->device ) );
+    const int w = s.L.w[octave], h = s.L.h[octave];
+    float* tmp = nullptr;
+    CU( cudaMalloc( &tmp, sizeof(float) * (size_t)w * h ) );
+    const float* lo = s.L.base[octave] + (size_t)level * s.L.lstride[octave];
+    cudaError_t e = launch_dog_plane( lo, lo + s.L.lstride[octave], tmp, w, h, s.L.pitch[octave], 0 );
+    if( e == cudaSuccess ) e = cudaMemcpy( out, tmp, sizeof(float) * (size_t)w * h, cudaMemcpyDeviceToHost );
+    cudaFree( tmp );
+    if( e != cudaSuccess ) return fail( PSIFT_E_CUDA, "dog readback: %s", cudaGetErrorString( e ) );
+    return PSIFT_OK;
+}
+
+int psift_last_timing( psift_ctx* c, float ms[8] )
+{
+    if( !c || !ms ) return fail( PSIFT_E_INVALID, "null argument" );
+    std::lock_guard<std::mutex> lk( c->mu );
+    memcpy( ms, c->last_ms, sizeof c->last_ms );
+    return PSIFT_OK;
+}
+
+long long psift_launch_count( psift_ctx* c ) { return c ? c->launches : 0; }
+
+} // extern "C"
