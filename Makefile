@@ -10,7 +10,10 @@ CU_SRCS  := $(CSRC)/k_pyramid.cu $(CSRC)/k_extrema.cu $(CSRC)/k_orient.cu $(CSRC
 CPP_SRCS := $(CSRC)/tables.cpp $(wildcard $(CSRC)/host/*.cpp)
 OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU_SRCS)) $(patsubst $(CSRC)/%.cpp,$(OBJDIR)/%.o,$(CPP_SRCS))
 
-all: $(LIB)
+all: $(LIB) tests/cpp/api_demo
+
+tests/cpp/api_demo: tests/cpp/api_demo.cpp $(LIB) $(wildcard include/popsift/*.h)
+	g++ -std=c++17 -O2 -Iinclude -o $@ $< -Lpopsift_b200 -lpopsift_b200 -Wl,-rpath,'$$ORIGIN/../../popsift_b200' -lpthread
 
 $(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/common.h $(CSRC)/kernels.h include/psift.h
 	@mkdir -p $(dir $@)

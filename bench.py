@@ -153,15 +153,14 @@ def main():
     import torch
     import torch.distributed as dist
     from popsift_b200 import capi
+    from popsift_b200 import dist as pdist
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the extraction path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    def barrier():
-        if world > 1: dist.barrier()
-        torch.cuda.synchronize()
+    barrier = pdist.barrier
 
     imgs = frames()
     dev_imgs = [torch.from_numpy(im).cuda() for im in imgs]
@@ -178,9 +177,8 @@ def main():
             a, b = run_stream(ctx, submit, src, BATCH); nf += a; nd += b
         barrier()
         dt = time.perf_counter() - t0
-        if world > 1:
-            t = torch.tensor([dt], device="cuda", dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX); dt = float(t.item())
-        return dt, nf, nd
+        dt = pdist.max_over_ranks(dt)
+        return dt, pdist.sum_over_ranks(nf) / world, pdist.sum_over_ranks(nd) / world
 
     l0 = ctx.launch_count()
     with ClockSampler(local) as cs:

@@ -1,0 +1,248 @@
+/* PopSift / SiftJob -- host-side job queue and multi-GPU dispatcher.
+ *
+ * Reference: src/popsift/popsift.cpp (constructor :16-38, configure :63-87, private_init :89-120,
+ * uninit :122-137, enqueue :139-169, uploadImages :171-180, extractDownloadLoop :182-213,
+ * SiftJob :238-313).  The reference runs two boost threads (upload, extract) around ONE pyramid
+ * on device 0.  Here there is one worker thread per GPU; each owns a psift context and keeps
+ * several frames in flight on it.  The image stream is sharded across GPUs by whichever worker
+ * dequeues a job first: no collective, no peer traffic, results come back through the job's
+ * own future.  All CUDA work goes through the C ABI (psift.h).
+ */
+#include <popsift/popsift.h>
+#include <psift.h>
+
+#include <condition_variable>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <iostream>
+#include <mutex>
+#include <thread>
+#include <atomic>
+
+using popsift::FeaturesHost;
+using popsift::FeaturesBase;
+
+/* ------------------------------------------------------------------ SiftJob */
+
+SiftJob::SiftJob( int w, int h, const unsigned char* imageData )
+    : _w( w ), _h( h ), _imageData( 0 ), _is_float( false ), _img( 0 )
+{
+    _f = _p.get_future();
+    const size_t n = (size_t)w * h;
+    _imageData = (unsigned char*)malloc( n ? n : 1 );
+    if( _imageData ) memcpy( _imageData, imageData, n );
+    else std::cerr << "popsift: SiftJob: out of memory for a " << w << "x" << h << " image" << std::endl;
+}
+
+SiftJob::SiftJob( int w, int h, const float* imageData )
+    : _w( w ), _h( h ), _imageData( 0 ), _is_float( true ), _img( 0 )
+{
+    _f = _p.get_future();
+    const size_t n = (size_t)w * h * sizeof(float);
+    _imageData = (unsigned char*)malloc( n ? n : 1 );
+    if( _imageData ) memcpy( _imageData, imageData, n );
+    else std::cerr << "popsift: SiftJob: out of memory for a " << w << "x" << h << " image" << std::endl;
+}
+
+SiftJob::~SiftJob( ) { free( _imageData ); }
+
+void SiftJob::setImg( popsift::ImageBase* img ) { _img = img; }
+popsift::ImageBase* SiftJob::getImg() { return _img; }
+void SiftJob::setFeatures( FeaturesBase* f ) { _p.set_value( f ); }
+FeaturesHost* SiftJob::get()     { return getHost(); }
+FeaturesBase* SiftJob::getBase() { return _f.get(); }
+FeaturesHost* SiftJob::getHost() { return dynamic_cast<FeaturesHost*>( _f.get() ); }
+popsift::FeaturesDev* SiftJob::getDev() { return dynamic_cast<popsift::FeaturesDev*>( _f.get() ); }
+
+/* ------------------------------------------------------------------ PopSift */
+
+static std::atomic<int> g_device_limit( 0 );
+
+struct PopSiftImpl
+{
+    std::mutex              mu;
+    std::condition_variable cv;
+    std::deque<SiftJob*>    queue;
+    bool                    stop = false;
+    bool                    started = false;
+    std::atomic<long>       processed{ 0 };
+    std::vector<psift_ctx*> ctx;
+    std::vector<std::thread> workers;
+    psift_config            cfg;
+    static const int        IN_FLIGHT = 3;
+
+    void worker( int idx );
+    static FeaturesHost* convert( const psift_result& r );
+};
+
+FeaturesHost* PopSiftImpl::convert( const psift_result& r )
+{
+    FeaturesHost* fh = new FeaturesHost( r.n_feat, r.n_desc );
+    if( fh->getFeatureCount() != r.n_feat ) return fh;
+    popsift::Descriptor* dbase = fh->getDescriptors();
+    if( r.n_desc > 0 ) memcpy( dbase, r.desc, sizeof(popsift::Descriptor) * (size_t)r.n_desc );
+    popsift::Feature* f = fh->getFeatures();
+    for( int i = 0; i < r.n_feat; i++ ) {
+        const psift_feature& s = r.feat[i];
+        f[i].debug_octave = s.debug_octave;
+        f[i].xpos = s.xpos; f[i].ypos = s.ypos; f[i].sigma = s.sigma; f[i].num_ori = s.num_ori;
+        for( int k = 0; k < ORIENTATION_MAX_COUNT; k++ ) {
+            f[i].orientation[k] = s.orientation[k];
+            f[i].desc[k] = ( s.desc_idx[k] >= 0 ) ? dbase + s.desc_idx[k] : 0;
+        }
+    }
+    return fh;
+}
+
+void PopSiftImpl::worker( int idx )
+{
+    psift_ctx* c = ctx[idx];
+    std::deque<std::pair<SiftJob*, psift_job*> > inflight;
+    for( ;; ) {
+        /* fill the pipeline: block only when nothing is in flight */
+        while( (int)inflight.size() < IN_FLIGHT ) {
+            SiftJob* job = 0;
+            {
+                std::unique_lock<std::mutex> lk( mu );
+                if( inflight.empty() ) cv.wait( lk, [&] { return stop || !queue.empty(); } );
+                if( !queue.empty() ) { job = queue.front(); queue.pop_front(); }
+            }
+            if( !job ) break;
+            psift_job* pj = 0;
+            int rc = job->data() == 0 ? PSIFT_E_INVALID
+                   : job->isFloat() ? psift_submit_f32( c, job->width(), job->height(), (const float*)job->data(), 0, &pj )
+                                    : psift_submit_u8 ( c, job->width(), job->height(), job->data(), 0, &pj );
+            if( rc != PSIFT_OK ) {
+                std::cerr << "popsift: extraction failed: " << psift_last_error() << std::endl;
+                job->setFeatures( new FeaturesHost( 0, 0 ) );
+                continue;
+            }
+            inflight.push_back( std::make_pair( job, pj ) );
+        }
+        if( inflight.empty() ) {
+            std::unique_lock<std::mutex> lk( mu );
+            if( stop && queue.empty() ) return;
+            continue;
+        }
+        /* retire the oldest frame */
+        SiftJob* job = inflight.front().first; psift_job* pj = inflight.front().second;
+        inflight.pop_front();
+        psift_result r;
+        FeaturesHost* fh;
+        if( psift_wait( pj, &r ) == PSIFT_OK ) {
+            fh = convert( r );
+            if( r.n_desc == 0 && r.n_feat != 0 ) std::cerr << "Warning: no descriptors extracted" << std::endl;
+        } else {
+            std::cerr << "popsift: extraction failed: " << psift_last_error() << std::endl;
+            fh = new FeaturesHost( 0, 0 );
+        }
+        psift_job_free( pj );
+        processed++;
+        job->setFeatures( fh );
+    }
+}
+
+void PopSift::setDeviceLimit( int n ) { g_device_limit = n; }
+
+PopSift::PopSift( ImageMode imode )
+    : _impl( new PopSiftImpl ), _last_init_w( 0 ), _last_init_h( 0 ), _image_mode( imode )
+{
+    configure( _config, true );
+}
+
+PopSift::PopSift( const popsift::Config& config, popsift::Config::ProcessingMode mode, ImageMode imode )
+    : _impl( new PopSiftImpl ), _last_init_w( 0 ), _last_init_h( 0 ), _image_mode( imode )
+{
+    if( mode == popsift::Config::MatchingMode )
+        std::cerr << "popsift: MatchingMode (device-resident features) is outside the extraction path; using ExtractingMode" << std::endl;
+    configure( config, true );
+}
+
+PopSift::~PopSift() { uninit(); delete _impl; }
+
+int PopSift::deviceCount() const { return (int)_impl->ctx.size(); }
+
+bool PopSift::configure( const popsift::Config& config, bool force )
+{
+    PopSiftImpl* I = _impl;
+    if( I->processed.load() > 0 && !force ) return false;          /* popsift.cpp:65-67 */
+    _config = config;
+    _config.levels = std::max( 2, config.levels );                   /* popsift.cpp:71 */
+    _config.toC( &I->cfg );
+    if( I->ctx.empty() ) {
+        int n = psift_device_count();
+        const char* env = getenv( "POPSIFT_NUM_GPUS" );
+        int lim = g_device_limit.load();
+        if( env && atoi( env ) > 0 ) lim = atoi( env );
+        if( lim > 0 && lim < n ) n = lim;
+        if( n <= 0 ) {
+            std::cerr << "popsift: no CUDA device found (this library has no CPU path)" << std::endl;
+            return false;
+        }
+        for( int d = 0; d < n; d++ ) {
+            psift_ctx* c = 0;
+            if( psift_create( d, &I->cfg, &c ) != PSIFT_OK ) {
+                std::cerr << "popsift: cannot create a context on device " << d << ": " << psift_last_error() << std::endl;
+                continue;
+            }
+            I->ctx.push_back( c );
+        }
+        if( I->ctx.empty() ) return false;
+        I->stop = false;
+        for( size_t k = 0; k < I->ctx.size(); k++ ) I->workers.emplace_back( &PopSiftImpl::worker, I, (int)k );
+        I->started = true;
+        return true;
+    }
+    /* re-configuration: drain first, contexts refuse while frames are in flight */
+    for( ;; ) {
+        { std::lock_guard<std::mutex> lk( I->mu ); if( I->queue.empty() ) break; }
+        std::this_thread::yield();
+    }
+    bool ok = true;
+    for( auto c : I->ctx ) {
+        int rc;
+        while( ( rc = psift_configure( c, &I->cfg ) ) == PSIFT_E_STATE ) std::this_thread::yield();
+        if( rc != PSIFT_OK ) { std::cerr << "popsift: configure failed: " << psift_last_error() << std::endl; ok = false; }
+    }
+    return ok;
+}
+
+void PopSift::uninit( )
+{
+    PopSiftImpl* I = _impl;
+    if( !I->started ) return;
+    { std::lock_guard<std::mutex> lk( I->mu ); I->stop = true; }
+    I->cv.notify_all();
+    for( auto& t : I->workers ) if( t.joinable() ) t.join();
+    I->workers.clear();
+    for( auto c : I->ctx ) psift_destroy( c );
+    I->ctx.clear();
+    I->started = false;
+}
+
+SiftJob* PopSift::enqueue( int w, int h, const unsigned char* imageData )
+{
+    if( _image_mode != ByteImages ) {
+        std::cerr << "popsift: image mode error: byte image sent to a PopSift object configured for float images" << std::endl;
+        return 0;                                                    /* the reference exits here, popsift.cpp:143-148 */
+    }
+    if( !_impl->started ) { std::cerr << "popsift: enqueue on an uninitialised PopSift object" << std::endl; return 0; }
+    SiftJob* job = new SiftJob( w, h, imageData );
+    { std::lock_guard<std::mutex> lk( _impl->mu ); _impl->queue.push_back( job ); }
+    _impl->cv.notify_one();
+    return job;
+}
+
+SiftJob* PopSift::enqueue( int w, int h, const float* imageData )
+{
+    if( _image_mode != FloatImages ) {
+        std::cerr << "popsift: image mode error: float image sent to a PopSift object configured for byte images" << std::endl;
+        return 0;
+    }
+    if( !_impl->started ) { std::cerr << "popsift: enqueue on an uninitialised PopSift object" << std::endl; return 0; }
+    SiftJob* job = new SiftJob( w, h, imageData );
+    { std::lock_guard<std::mutex> lk( _impl->mu ); _impl->queue.push_back( job ); }
+    _impl->cv.notify_one();
+    return job;
+}
