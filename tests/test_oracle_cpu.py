@@ -1,0 +1,48 @@
+"""Pins the CPU oracle (oracle/cpu_sift.cpp) against the outputs of the reference's own CUDA build
+(tests/golden/ref, generated on a B200 by tools/run_ref_golden.py from tests/golden/inputs)."""
+import os, subprocess
+import numpy as np
+import pytest
+import refio, parity
+from tools import golden_cases as gc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "oracle", "cpu_sift")
+SKIP_FLAGS = {"iloop"}                       # not restated
+CASES = [c for c, (_, flags, _) in gc.CASES.items()
+         if os.path.exists(os.path.join(refio.GOLD, "ref", c + ".feat.bin")) and not (set(flags) & SKIP_FLAGS)]
+# bilinear float textures (igrid/notile) are blended in float on the CPU: descriptor tolerance is looser there
+DESC_TOL = {"g256_vlfeat_igrid": 2e-2, "g256_notile": 2e-2, "g256_grid": 5e-2}
+
+
+@pytest.fixture(scope="module", autouse=True)
+def build_oracle():
+    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, capture_output=True)
+
+
+def run_oracle(tmp_path, case):
+    img, flags, planes = gc.CASES[case]
+    w, h, _ = gc.IMAGES[img]
+    out = str(tmp_path / case)
+    cmd = [EXE, "--in", gc.image_path(img), "--w", str(w), "--h", str(h), "--out", out, "--quiet"] + flags + (["--dump-planes"] if planes else [])
+    subprocess.run(cmd, check=True, timeout=600)
+    return out
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_oracle_matches_reference_cuda_output(tmp_path, case):
+    out = run_oracle(tmp_path, case)
+    mine, ref = refio.RefFeatures(out + ".feat.bin"), refio.RefFeatures(os.path.join(refio.GOLD, "ref", case + ".feat.bin"))
+    flags = gc.CASES[case][1]
+    nm = int(flags[flags.index("--norm-multi") + 1]) if "--norm-multi" in flags else 0
+    rep = parity.compare(mine, ref, norm_multi=nm)
+    assert rep["ok_int"], rep                         # counts, octave, level, num_ori
+    assert rep["xy_bitexact"], rep                    # refinement is +,-,*,fma,1/x only: exact on the CPU too
+    assert rep["max_dsigma_rel"] < 1e-6, rep          # powf: CUDA vs libm
+    assert rep["max_dtheta"] < parity.TOL_THETA, rep
+    assert rep["max_desc_l2"] < DESC_TOL.get(case, parity.TOL_DESC), rep
+    if gc.CASES[case][2]:
+        a, b = refio.RefPlanes(out + ".planes.bin"), refio.RefPlanes(os.path.join(refio.GOLD, "ref", case + ".planes.bin"))
+        for o in range(b.n_octaves):
+            assert np.array_equal(a.gauss[o].view(np.uint32), b.gauss[o].view(np.uint32)), "Gaussian planes of octave %d" % o
+            assert np.array_equal(a.dog[o].view(np.uint32), b.dog[o].view(np.uint32)), "DoG planes of octave %d" % o

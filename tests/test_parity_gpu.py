@@ -172,3 +172,29 @@ def test_cpp_api_demo_matches_golden(tmp_path):
     d = max(np.linalg.norm(desc[a["desc_idx"][i][k]] - ref.desc[c["desc_idx"][i][k]])
             for i in range(nf) for k in range(a["num_ori"][i]) if c["desc_idx"][i][k] != ref.n_desc - 1)
     assert d < parity.TOL_DESC
+
+
+ORACLE = os.path.join(ROOT, "oracle", "cpu_sift")
+ORACLE_CASES = [(200, 150, 21, []), (97, 131, 22, []), (320, 240, 23, ["--mode", "vlfeat", "--desc-mode", "grid"]),
+                (161, 243, 24, ["--downsampling", "0", "--norm-mode", "classic"]), (128, 128, 25, ["--mode", "opencv", "--gauss-mode", "opencv"]),
+                (300, 200, 26, ["--levels", "5"]), (64, 256, 27, ["--sigma", "1.2", "--threshold", "0.02", "--edge-threshold", "8"])]
+
+
+@pytest.mark.skipif(not os.path.exists(ORACLE), reason="oracle/cpu_sift not built")
+@pytest.mark.parametrize("w,h,seed,flags", ORACLE_CASES)
+def test_cuda_path_against_cpu_oracle(tmp_path, w, h, seed, flags):
+    """Fresh seeded inputs (not in the golden set): CUDA path vs the pinned CPU oracle."""
+    img = synth.gen(w, h, seed)
+    p = tmp_path / "in.u8"; img.tofile(p)
+    out = str(tmp_path / "o")
+    subprocess.run([ORACLE, "--in", str(p), "--w", str(w), "--h", str(h), "--out", out, "--quiet", "--dump-planes"] + flags, check=True, timeout=600)
+    ora = refio.RefFeatures(out + ".feat.bin")
+    cfg = capi.config_from_flags(flags)
+    with capi.Context(cfg) as ctx:
+        mine = ctx.extract(img)
+        rep = parity.compare(mine, ora, norm_multi=cfg.norm_multi, skip_last_desc=False)
+        n, nb, mx = parity.compare_planes(ctx, refio.RefPlanes(out + ".planes.bin"))
+    assert n == nb, (n, nb, mx)                       # every Gaussian and DoG plane bit-exact
+    assert rep["ok_int"] and rep["xy_bitexact"], rep
+    assert rep["max_dsigma_rel"] < 1e-6 and rep["max_dtheta"] < parity.TOL_THETA, rep
+    assert rep["max_desc_l2"] < (0.05 if "grid" in flags else parity.TOL_DESC), rep
