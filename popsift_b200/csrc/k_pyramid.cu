@@ -24,6 +24,7 @@
  */
 #include "common.h"
 #include "kernels.h"
+#include <cstdlib>
 
 namespace psift {
 
@@ -160,6 +161,247 @@ k_blur_level( const __grid_constant__ BlurArgs a )
     }
 }
 
+
+/* ------------------------------------------------------------------------------------------
+ * v2: exact tap count (template on H = span-1), packed fp32x2 arithmetic (FFMA2/FADD2, new on
+ * sm_100) and a 128x64 tile.  The horizontal pass works on PAIRS OF ROWS: the staged source is
+ * stored row-pair interleaved ((r,c),(r+1,c) adjacent), so one 64-bit register pair holds the same
+ * column of two rows and every tap is one FADD2 + one FFMA2 for two outputs.  The vertical pass
+ * works on PAIRS OF COLUMNS out of the row-major intermediate.  Per-element rounding of the packed
+ * instructions is IEEE round-to-nearest, identical to the scalar FADD/FFMA sequence above, and the
+ * tap order is unchanged, so the planes stay bit-identical (tests/test_parity_gpu.py).
+ * ------------------------------------------------------------------------------------------ */
+/* Two tile shapes: BIG for planes that fill the GPU, SMALL for the deeper octaves, where more and
+ * shorter blocks cut the latency of each (dependent) level. */
+struct TileBig   { static constexpr int TXv = 128, TYv = 64, VYv = 8; };
+struct TileSmall { static constexpr int TXv = 64,  TYv = 32, VYv = 4; };
+
+__device__ __forceinline__ float2 ffma2( float2 a, float b, float2 c )
+{
+    float2 d;
+    asm( "{ .reg .b64 ra, rb, rc, rd;\n"
+         "  mov.b64 ra, {%2, %3};\n  mov.b64 rb, {%4, %4};\n  mov.b64 rc, {%5, %6};\n"
+         "  fma.rn.f32x2 rd, ra, rb, rc;\n  mov.b64 {%0, %1}, rd; }"
+         : "=f"( d.x ), "=f"( d.y ) : "f"( a.x ), "f"( a.y ), "f"( b ), "f"( c.x ), "f"( c.y ) );
+    return d;
+}
+__device__ __forceinline__ float2 fadd2( float2 a, float2 b )
+{
+    float2 d;
+    asm( "{ .reg .b64 ra, rb, rd;\n"
+         "  mov.b64 ra, {%2, %3};\n  mov.b64 rb, {%4, %5};\n"
+         "  add.rn.f32x2 rd, ra, rb;\n  mov.b64 {%0, %1}, rd; }"
+         : "=f"( d.x ), "=f"( d.y ) : "f"( a.x ), "f"( a.y ), "f"( b.x ), "f"( b.y ) );
+    return d;
+}
+__device__ __forceinline__ float2 fmul2( float2 a, float b )
+{
+    float2 d;
+    asm( "{ .reg .b64 ra, rb, rd;\n"
+         "  mov.b64 ra, {%2, %3};\n  mov.b64 rb, {%4, %4};\n"
+         "  mul.rn.f32x2 rd, ra, rb;\n  mov.b64 {%0, %1}, rd; }"
+         : "=f"( d.x ), "=f"( d.y ) : "f"( a.x ), "f"( a.y ), "f"( b ) );
+    return d;
+}
+
+template<int H, bool FROM_TEX, class T>
+__global__ void __launch_bounds__( NT, 2 )
+k_blur2( const __grid_constant__ BlurArgs a )
+{
+    constexpr int TXv = T::TXv, TYv = T::TYv, VYv = T::VYv;
+    constexpr int HX  = ( H + 3 ) / 4 * 4;          /* x halo, padded so that staged rows stay 16-byte aligned */
+    constexpr int SW  = TXv + 2 * HX;                /* staged width */
+    constexpr int SQ  = SW / 4;                      /* 16-byte chunks (2 columns x 2 rows) per half row */
+    constexpr int RP  = TYv / 2 + H;                 /* staged row pairs */
+    constexpr int D   = HX - H;
+    constexpr int W0  = D & ~1;                      /* first window element (even: whole chunks) */
+    constexpr int E0  = D & 1;
+    constexpr int WN  = ( 4 + 2 * H + E0 + 1 ) & ~1; /* window length in float2, even */
+    extern __shared__ __align__( 16 ) float smem[];
+    /* S4[p][..]: row pair p as 16-byte chunks {(2p,2c),(2p+1,2c),(2p,2c+1),(2p+1,2c+1)}; the even
+     * chunks of a row come first, then the odd ones, so that a warp whose lanes are two chunks
+     * apart reads consecutive 16-byte words (no bank conflict). */
+    float4* S4 = reinterpret_cast<float4*>( smem );  /* [RP][2*SQ] */
+    float*  I  = smem + 2 * RP * SW;                  /* [2*RP][TXv]  horizontal result, row-major */
+
+    const int tid = threadIdx.x;
+    const int tx0 = blockIdx.x * TXv, ty0 = blockIdx.y * TYv;
+    const int w = a.w, h = a.h;
+    const int nrow = min( TYv, h - ty0 );            /* output rows / columns this tile really has */
+    const int ncol = min( TXv, w - tx0 );
+    const int RPn  = ( nrow + 2 * H + 1 ) >> 1;
+    const int ng   = ( ncol + 3 ) >> 2;              /* groups of 4 output columns */
+    const int SWn  = 2 * HX + 4 * ng;
+
+    /* ---- stage (clamp to edge) ---- */
+    if( FROM_TEX || tx0 - HX < 0 || tx0 + TXv + HX > w ) {
+        float2* S2 = reinterpret_cast<float2*>( smem );
+        const float fw = (float)w, fh = (float)h;
+        /* four independent fetches in flight per thread before the first store */
+        for( int i0 = tid; i0 < RPn * SW; i0 += 4 * NT ) {
+            float2 v[4];
+            #pragma unroll
+            for( int u = 0; u < 4; u++ ) {
+                const int i = min( i0 + u * NT, RPn * SW - 1 );
+                const int p = i / SW, c = i % SW;
+                const int g0 = min( max( ty0 - H + 2 * p,     0 ), h - 1 );
+                const int g1 = min( max( ty0 - H + 2 * p + 1, 0 ), h - 1 );
+                if( FROM_TEX ) {
+                    const int gx = tx0 - HX + c;                        /* x unclamped: see k_blur_level */
+                    const float rx = __fdiv_rn( (float)gx + a.shift, fw );
+                    v[u] = make_float2( tex2D<float>( a.tex, rx, __fdiv_rn( (float)g0 + a.shift, fh ) ),
+                                        tex2D<float>( a.tex, rx, __fdiv_rn( (float)g1 + a.shift, fh ) ) );
+                } else {
+                    const int gx = min( max( tx0 - HX + c, 0 ), w - 1 );
+                    v[u] = make_float2( __ldg( a.src + (size_t)g0 * a.pitch + gx ), __ldg( a.src + (size_t)g1 * a.pitch + gx ) );
+                }
+            }
+            #pragma unroll
+            for( int u = 0; u < 4; u++ ) {
+                const int i = i0 + u * NT;
+                const int p = i / SW, c = i % SW, ch = c >> 1;
+                if( i < RPn * SW && c < SWn )
+                    S2[( p * 2 * SQ + ( ch & 1 ) * SQ + ( ch >> 1 ) ) * 2 + ( c & 1 )] = v[u];
+            }
+        }
+    } else {
+        #pragma unroll 4
+        for( int i = tid; i < RPn * SQ; i += NT ) {
+            const int p = i / SQ, c4 = i % SQ;
+            const int g0 = min( max( ty0 - H + 2 * p,     0 ), h - 1 );
+            const int g1 = min( max( ty0 - H + 2 * p + 1, 0 ), h - 1 );
+            const float4 A = __ldg( reinterpret_cast<const float4*>( a.src + (size_t)g0 * a.pitch + ( tx0 - HX ) ) + c4 );
+            const float4 B = __ldg( reinterpret_cast<const float4*>( a.src + (size_t)g1 * a.pitch + ( tx0 - HX ) ) + c4 );
+            S4[p * 2 * SQ + c4]      = make_float4( A.x, B.x, A.y, B.y );
+            S4[p * 2 * SQ + SQ + c4] = make_float4( A.z, B.z, A.w, B.w );
+        }
+    }
+    __syncthreads();
+
+    /* ---- horizontal pass: 4 columns x 2 rows per thread ---- */
+    for( int i = tid; i < RPn * ( TXv / 4 ); i += NT ) {
+        const int p = i / ( TXv / 4 );
+        const int g = i % ( TXv / 4 );
+        if( g >= ng ) continue;
+        float2 win[WN];
+        const float4* src = S4 + p * 2 * SQ + g;
+        #pragma unroll
+        for( int k = 0; k < WN / 2; k++ ) {
+            constexpr int C = W0 / 2;
+            const float4 v = src[( ( C + k ) & 1 ) * SQ + ( ( C + k ) >> 1 )];
+            win[2 * k] = make_float2( v.x, v.y ); win[2 * k + 1] = make_float2( v.z, v.w );
+        }
+        float2 o[4];
+        #pragma unroll
+        for( int j = 0; j < 4; j++ ) {
+            constexpr int C0 = E0 + H;
+            float2 acc;
+            if( FROM_TEX ) {
+                acc = make_float2( 0.0f, 0.0f );
+                #pragma unroll
+                for( int off = H; off > 0; off-- ) acc = ffma2( fadd2( win[C0 + j - off], win[C0 + j + off] ), a.th.g[off], acc );
+                acc = ffma2( win[C0 + j], a.th.g[0], acc );
+                acc = fmul2( acc, 255.0f );
+            } else {
+                acc = ffma2( win[C0 + j], a.th.g[0], make_float2( 0.0f, 0.0f ) );
+                #pragma unroll
+                for( int off = H; off > 0; off-- ) acc = ffma2( fadd2( win[C0 + j - off], win[C0 + j + off] ), a.th.g[off], acc );
+            }
+            o[j] = acc;
+        }
+        *reinterpret_cast<float4*>( I + ( 2 * p     ) * TXv + 4 * g ) = make_float4( o[0].x, o[1].x, o[2].x, o[3].x );
+        *reinterpret_cast<float4*>( I + ( 2 * p + 1 ) * TXv + 4 * g ) = make_float4( o[0].y, o[1].y, o[2].y, o[3].y );
+    }
+    __syncthreads();
+
+    /* ---- vertical pass: 2 columns x VYv rows per thread ---- */
+    for( int i = tid; i < ( TXv / 2 ) * ( TYv / VYv ); i += NT ) {
+        const int cp = i % ( TXv / 2 );
+        const int y0 = ( i / ( TXv / 2 ) ) * VYv;
+        const int gx = tx0 + 2 * cp;
+        if( y0 >= nrow || gx >= w ) continue;
+        float2 win[VYv + 2 * H];
+        #pragma unroll
+        for( int k = 0; k < VYv + 2 * H; k++ ) win[k] = *reinterpret_cast<const float2*>( I + ( y0 + k ) * TXv + 2 * cp );
+        #pragma unroll
+        for( int j = 0; j < VYv; j++ ) {
+            float2 acc = make_float2( 0.0f, 0.0f );
+            #pragma unroll
+            for( int off = H; off > 0; off-- ) {
+                acc = ffma2( win[H + j - off], a.tv.g[off], acc );
+                acc = ffma2( win[H + j + off], a.tv.g[off], acc );
+            }
+            acc = ffma2( win[H + j], a.tv.g[0], acc );
+            const int gy = ty0 + y0 + j;
+            if( gy < h ) {
+                float* row = a.dst + (size_t)gy * a.pitch + gx;
+                if( gx + 1 < w ) *reinterpret_cast<float2*>( row ) = acc; else row[0] = acc.x;
+                if( a.ds_dst && !( gy & 1 ) ) a.ds_dst[(size_t)( gy >> 1 ) * a.ds_pitch + ( gx >> 1 )] = acc.x;
+            }
+        }
+    }
+}
+
+static long blur_small_max()
+{
+    static long v = -1;
+    if( v < 0 ) { const char* e = getenv( "PSIFT_BLUR_SMALL_MAX" ); v = e ? atol( e ) : 1024L * 600L; }
+    return v;
+}
+
+template<int H, bool FROM_TEX, class T>
+static cudaError_t launch_v2t( const BlurArgs& a, cudaStream_t st )
+{
+    constexpr int HX = ( H + 3 ) / 4 * 4;
+    constexpr int RP = T::TYv / 2 + H;
+    const size_t smem = sizeof(float) * ( (size_t)2 * RP * ( T::TXv + 2 * HX ) + (size_t)2 * RP * T::TXv );
+    static bool attr_done[16] = { false };
+    int dev = 0; cudaGetDevice( &dev );
+    if( dev >= 16 || !attr_done[dev] ) {
+        cudaError_t e = cudaFuncSetAttribute( k_blur2<H, FROM_TEX, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem );
+        if( e != cudaSuccess ) return e;
+        if( dev < 16 ) attr_done[dev] = true;
+    }
+    dim3 grid( ( a.w + T::TXv - 1 ) / T::TXv, ( a.h + T::TYv - 1 ) / T::TYv );
+    k_blur2<H, FROM_TEX, T><<<grid, NT, smem, st>>>( a );
+    return cudaGetLastError();
+}
+
+template<int H, bool FROM_TEX>
+static cudaError_t launch_v2( const BlurArgs& a, cudaStream_t st )
+{
+    if( (long)a.w * a.h <= blur_small_max() ) return launch_v2t<H, FROM_TEX, TileSmall>( a, st );
+    return launch_v2t<H, FROM_TEX, TileBig>( a, st );
+}
+
+template<bool FROM_TEX>
+static cudaError_t launch_blur_v2( const BlurArgs& a, cudaStream_t st, bool& handled )
+{
+    handled = true;
+    /* one template parameter serves both passes; a config whose two tables differ in length
+     * (never the case for the built-in Gauss modes) takes the generic kernel */
+    if( a.th.span != a.tv.span ) { handled = false; return cudaSuccess; }
+    switch( a.tv.span - 1 ) {
+    case 1:  return launch_v2<1,  FROM_TEX>( a, st );
+    case 2:  return launch_v2<2,  FROM_TEX>( a, st );
+    case 3:  return launch_v2<3,  FROM_TEX>( a, st );
+    case 4:  return launch_v2<4,  FROM_TEX>( a, st );
+    case 5:  return launch_v2<5,  FROM_TEX>( a, st );
+    case 6:  return launch_v2<6,  FROM_TEX>( a, st );
+    case 7:  return launch_v2<7,  FROM_TEX>( a, st );
+    case 8:  return launch_v2<8,  FROM_TEX>( a, st );
+    case 9:  return launch_v2<9,  FROM_TEX>( a, st );
+    case 10: return launch_v2<10, FROM_TEX>( a, st );
+    case 11: return launch_v2<11, FROM_TEX>( a, st );
+    case 12: return launch_v2<12, FROM_TEX>( a, st );
+    case 13: return launch_v2<13, FROM_TEX>( a, st );
+    case 14: return launch_v2<14, FROM_TEX>( a, st );
+    case 15: return launch_v2<15, FROM_TEX>( a, st );
+    case 16: return launch_v2<16, FROM_TEX>( a, st );
+    default: handled = false; return cudaSuccess;
+    }
+}
+
 template<int HQ, bool FROM_TEX>
 static cudaError_t launch_hq( const BlurArgs& a, cudaStream_t st )
 {
@@ -182,6 +424,9 @@ static cudaError_t launch_hq( const BlurArgs& a, cudaStream_t st )
 template<bool FROM_TEX>
 static cudaError_t launch_blur( const BlurArgs& a, cudaStream_t st )
 {
+    bool handled = false;
+    cudaError_t e2 = launch_blur_v2<FROM_TEX>( a, st, handled );
+    if( handled ) return e2;
     const int halo = max( a.th.span, a.tv.span ) - 1;
     const int hq   = max( 1, ( halo + 3 ) / 4 );
     switch( hq ) {
