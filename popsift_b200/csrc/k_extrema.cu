@@ -187,57 +187,142 @@ struct ExtGrid {
     int tiles_x[MAX_OCT];
 };
 
-constexpr int EX_TX = 32, EX_TY = 8;
+constexpr int EX_TX = 64, EX_TY = 16, EX_NT = 256;
+constexpr int EX_SW = EX_TX + 4;           /* DoG tile row: 1 halo column each side, padded to 68 */
+constexpr int EX_SH = EX_TY + 2;
 
-template<int MODE>
-__global__ void __launch_bounds__( EX_TX * EX_TY )
+static size_t extrema_smem( int n_lvl )
+{
+    return sizeof(float) * (size_t)( n_lvl - 1 ) * EX_SH * EX_SW                  /* DoG tile            */
+         + sizeof(unsigned short) * 2 * (size_t)( n_lvl - 3 ) * EX_TX * EX_TY;    /* two survivor queues */
+}
+
+/* One block = one 64x16 tile of one octave, all levels.
+ *   load    : every Gaussian level of the tile (+1 halo) is read once, coalesced; the DoG goes to smem
+ *   phase 1 : first contrast test on each voxel's own value; survivors are queued (warp-aggregated)
+ *   phase 2 : 26-neighbour test out of shared memory, balanced over the block; strict extrema queued
+ *   phase 3 : Newton refinement for the few that are left (neighbours re-derived from the
+ *             L2-resident Gaussian planes, since the iteration may walk out of the tile)
+ * NLVL > 0 fixes the number of Gaussian levels at compile time (all loads of a pixel in flight
+ * together); NLVL == 0 takes it from the layout. */
+template<int MODE, int NLVL>
+__global__ void __launch_bounds__( EX_NT )
 k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid G, const __grid_constant__ Consts K,
            Cand* cand, int cand_stride, Counters* ct )
 {
+    extern __shared__ __align__( 16 ) float ex_smem[];
+    __shared__ int n1, n2;
+    const int n_lvl = NLVL ? NLVL : L.n_lvl;
+    const int qcap  = ( n_lvl - 3 ) * EX_TX * EX_TY;
+    float*          D  = ex_smem;                                             /* [n_lvl-1][EX_SH][EX_SW] */
+    unsigned short* q1 = reinterpret_cast<unsigned short*>( D + ( n_lvl - 1 ) * EX_SH * EX_SW );
+    unsigned short* q2 = q1 + qcap;
+
     int o = 0;
     while( o + 1 < L.n_oct && (int)blockIdx.x >= G.first_block[o + 1] ) o++;
     const int tile = blockIdx.x - G.first_block[o];
     const int w = L.w[o], h = L.h[o];
-    const int x = ( tile % G.tiles_x[o] ) * EX_TX + threadIdx.x + 1;
-    const int y = ( tile / G.tiles_x[o] ) * EX_TY + threadIdx.y + 1;
+    const int tx0 = ( tile % G.tiles_x[o] ) * EX_TX;
+    const int ty0 = ( tile / G.tiles_x[o] ) * EX_TY;
+    const int tid = threadIdx.x;
+    if( tid == 0 ) { n1 = 0; n2 = 0; }
 
     DogView dv;
-    dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = L.n_lvl;
+    dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = n_lvl;
 
-    bool inside = ( x <= w - 2 ) && ( y <= h - 2 );
-    if( MODE == PSIFT_MODE_OPENCV ) inside = inside && !( x < 5 || y < 5 || x >= w - 5 || y >= h - 5 );   /* :336-340 */
-
-    const float w_div = __fdiv_rn( (float)w, (float)K.grid_size );
-    const float h_div = __fdiv_rn( (float)h, (float)K.grid_size );
-
-    /* Gaussian column: G[1..nlvl-2] give the inner DoG levels' centre values */
-    float g_prev = 0.f;
-    const float* col = dv.base + (size_t)y * dv.pitch + x;
-    if( inside ) g_prev = __ldg( col + dv.lstride );
-    for( int level = 1; level <= L.n_lvl - 3; level++ ) {
-        bool found = false;
-        Cand c;
-        if( inside ) {
-            const float g_next = __ldg( col + (size_t)( level + 1 ) * dv.lstride );
-            const float val = __fsub_rn( g_next, g_prev );
-            g_prev = g_next;
-            if( first_contrast_ok<MODE>( val, K.threshold ) && strict_extremum( dv, x, y, level, val ) ) {
-                found = refine_extremum<MODE>( dv, K, x, y, level, val, w_div, h_div, c );
-                if( found ) {
-                    c.key_lo = (uint32_t)x | ( (uint32_t)( y & 0xf ) << 28 );
-                    c.key_hi = ( (uint32_t)y >> 4 ) | ( (uint32_t)level << 24 );
-                }
+    /* ---- load: Gaussian levels -> DoG tile ---- */
+    constexpr int LW = EX_TX + 2;
+    for( int i = tid; i < EX_SH * LW; i += EX_NT ) {
+        const int sy = i / LW, sx = i % LW;
+        const int gx = min( max( tx0 - 1 + sx, 0 ), w - 1 );
+        const int gy = min( max( ty0 - 1 + sy, 0 ), h - 1 );
+        const float* p = dv.base + (size_t)gy * dv.pitch + gx;
+        float* d = D + sy * EX_SW + sx;
+        if( NLVL ) {
+            float g[NLVL ? NLVL : 1];
+            #pragma unroll
+            for( int l = 0; l < NLVL; l++ ) g[l] = __ldg( p + (size_t)l * dv.lstride );
+            #pragma unroll
+            for( int l = 0; l + 1 < NLVL; l++ ) d[l * EX_SH * EX_SW] = __fsub_rn( g[l + 1], g[l] );
+        } else {
+            float prev = __ldg( p );
+            for( int l = 1; l < n_lvl; l++ ) {
+                const float cur = __ldg( p + (size_t)l * dv.lstride );
+                d[( l - 1 ) * EX_SH * EX_SW] = __fsub_rn( cur, prev );
+                prev = cur;
             }
         }
-        /* warp-aggregated append (s_extrema.cu:22-44) */
-        const unsigned mask = __ballot_sync( 0xffffffffu, found );
-        if( mask ) {
-            const int lane = threadIdx.x & 31;
-            int base = 0;
-            if( lane == 0 ) base = atomicAdd( &ct->ext_ct[o], __popc( mask ) );
-            base = __shfl_sync( 0xffffffffu, base, 0 );
-            const int idx = base + __popc( mask & ( ( 1u << lane ) - 1 ) );
-            if( found && idx < K.max_extrema ) cand[(size_t)o * cand_stride + idx] = c;
+    }
+    __syncthreads();
+
+    /* ---- phase 1: first contrast test ---- */
+    const int lane = tid & 31;
+    #pragma unroll
+    for( int k = 0; k < EX_TX * EX_TY / EX_NT; k++ ) {
+        const int idx = tid + k * EX_NT;
+        const int x = idx % EX_TX, y = idx / EX_TX;
+        const int gx = tx0 + x, gy = ty0 + y;
+        bool inside = ( gx >= 1 ) && ( gy >= 1 ) && ( gx <= w - 2 ) && ( gy <= h - 2 );
+        if( MODE == PSIFT_MODE_OPENCV ) inside = inside && !( gx < 5 || gy < 5 || gx >= w - 5 || gy >= h - 5 );   /* :336-340 */
+        for( int level = 1; level <= n_lvl - 3; level++ ) {
+            const float v = D[( level * EX_SH + y + 1 ) * EX_SW + x + 1];
+            const bool pass = inside && first_contrast_ok<MODE>( v, K.threshold );
+            const unsigned mask = __ballot_sync( 0xffffffffu, pass );
+            if( mask ) {
+                int base = 0;
+                if( lane == 0 ) base = atomicAdd( &n1, __popc( mask ) );
+                base = __shfl_sync( 0xffffffffu, base, 0 );
+                if( pass ) q1[base + __popc( mask & ( ( 1u << lane ) - 1 ) )] = (unsigned short)( x | ( y << 6 ) | ( level << 10 ) );
+            }
+        }
+    }
+    __syncthreads();
+
+    /* ---- phase 2: strict maximum or minimum of the 26 neighbours (s_extrema.cu:56-120) ---- */
+    const int cnt1 = n1;
+    for( int i = tid; i < cnt1; i += EX_NT ) {
+        const unsigned e = q1[i];
+        const int x = e & 63, y = ( e >> 6 ) & 15, level = e >> 10;
+        const float* c = D + ( level * EX_SH + y + 1 ) * EX_SW + x + 1;
+        const float v = *c;
+        bool gt = true, lt = true;
+        #pragma unroll
+        for( int dy = -1; dy <= 1; dy++ )
+            #pragma unroll
+            for( int dx = -1; dx <= 1; dx++ ) {
+                if( dy == 0 && dx == 0 ) continue;
+                const float f = c[dy * EX_SW + dx];
+                gt = gt && ( v > f ); lt = lt && ( v < f );
+            }
+        if( !gt && !lt ) continue;
+        #pragma unroll
+        for( int dz = -1; dz <= 1; dz += 2 )
+            #pragma unroll
+            for( int dy = -1; dy <= 1; dy++ )
+                #pragma unroll
+                for( int dx = -1; dx <= 1; dx++ ) {
+                    const float f = c[dz * EX_SH * EX_SW + dy * EX_SW + dx];
+                    gt = gt && ( v > f ); lt = lt && ( v < f );
+                }
+        if( gt || lt ) q2[atomicAdd( &n2, 1 )] = (unsigned short)e;
+    }
+    __syncthreads();
+
+    /* ---- phase 3: refinement ---- */
+    const int cnt2 = n2;
+    if( cnt2 == 0 ) return;
+    const float w_div = __fdiv_rn( (float)w, (float)K.grid_size );
+    const float h_div = __fdiv_rn( (float)h, (float)K.grid_size );
+    for( int i = tid; i < cnt2; i += EX_NT ) {
+        const unsigned e = q2[i];
+        const int x = tx0 + ( e & 63 ), y = ty0 + ( ( e >> 6 ) & 15 ), level = e >> 10;
+        const float val = D[( level * EX_SH + ( y - ty0 ) + 1 ) * EX_SW + ( x - tx0 ) + 1];
+        Cand c;
+        if( refine_extremum<MODE>( dv, K, x, y, level, val, w_div, h_div, c ) ) {
+            c.key_lo = (uint32_t)x | ( (uint32_t)( y & 0xf ) << 28 );
+            c.key_hi = ( (uint32_t)y >> 4 ) | ( (uint32_t)level << 24 );
+            const int idx = atomicAdd( &ct->ext_ct[o], 1 );                 /* append, s_extrema.cu:22-44 */
+            if( idx < K.max_extrema ) cand[(size_t)o * cand_stride + idx] = c;
         }
     }
 }
@@ -295,18 +380,29 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     int nb = 0;
     for( int o = 0; o < L.n_oct; o++ ) {
         G.first_block[o] = nb;
-        const int tx = ( max( L.w[o] - 2, 1 ) + EX_TX - 1 ) / EX_TX;
-        const int ty = ( max( L.h[o] - 2, 1 ) + EX_TY - 1 ) / EX_TY;
+        const int tx = ( L.w[o] + EX_TX - 1 ) / EX_TX;
+        const int ty = ( L.h[o] + EX_TY - 1 ) / EX_TY;
         G.tiles_x[o] = tx;
         nb += tx * ty;
     }
     for( int o = L.n_oct; o <= MAX_OCT; o++ ) G.first_block[o] = nb;
-    dim3 block( EX_TX, EX_TY );
+    const size_t smem = extrema_smem( L.n_lvl );
+    if( L.n_lvl > 60 ) return cudaErrorInvalidValue;                      /* queue entries hold 6 bits of level */
+#define PSIFT_EXT_LAUNCH( MODE )                                                                             \
+    do {                                                                                                      \
+        if( L.n_lvl == 6 ) k_extrema<MODE, 6><<<nb, EX_NT, smem, st>>>( L, G, K, cand, cand_stride, ct );      \
+        else {                                                                                                \
+            cudaError_t e = cudaFuncSetAttribute( k_extrema<MODE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem ); \
+            if( e != cudaSuccess ) return e;                                                                  \
+            k_extrema<MODE, 0><<<nb, EX_NT, smem, st>>>( L, G, K, cand, cand_stride, ct );                     \
+        }                                                                                                     \
+    } while( 0 )
     switch( K.sift_mode ) {
-    case PSIFT_MODE_OPENCV: k_extrema<PSIFT_MODE_OPENCV><<<nb, block, 0, st>>>( L, G, K, cand, cand_stride, ct ); break;
-    case PSIFT_MODE_VLFEAT: k_extrema<PSIFT_MODE_VLFEAT><<<nb, block, 0, st>>>( L, G, K, cand, cand_stride, ct ); break;
-    default:                k_extrema<PSIFT_MODE_POPSIFT><<<nb, block, 0, st>>>( L, G, K, cand, cand_stride, ct ); break;
+    case PSIFT_MODE_OPENCV: PSIFT_EXT_LAUNCH( PSIFT_MODE_OPENCV ); break;
+    case PSIFT_MODE_VLFEAT: PSIFT_EXT_LAUNCH( PSIFT_MODE_VLFEAT ); break;
+    default:                PSIFT_EXT_LAUNCH( PSIFT_MODE_POPSIFT ); break;
     }
+#undef PSIFT_EXT_LAUNCH
     k_extrema_finish<<<1, 32, 0, st>>>( ct, L.n_oct, K.max_extrema, ext_capacity );
     k_rank_sort<<<dim3( 8, L.n_oct ), RS_NT, 0, st>>>( cand, cand_stride, ct, L.n_oct, sorted );
     if( launches ) *launches += 3;
