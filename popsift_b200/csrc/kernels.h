@@ -14,7 +14,7 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
 cudaError_t launch_orientation( const PyrLayout& L, const Cand* sorted, Counters* ct, psift_extremum* ext,
                                 int* desc_map, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches );
 /* k_desc.cu */
-cudaError_t launch_descriptors( const PyrLayout& L, const Consts& K, const psift_extremum* ext, const Counters* ct,
+cudaError_t launch_descriptors( const PyrLayout& L, const Consts& K, const psift_extremum* ext, Counters* ct,
                                 const int* desc_map, const cudaTextureObject_t* lintex, const DescTables* tab,
                                 float* desc, psift_feature* feat, int n_blocks, cudaStream_t st, long long* launches );
 /* pipeline.cu helper kernel: DoG plane for the parity hook */
