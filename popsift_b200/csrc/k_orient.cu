@@ -21,15 +21,8 @@ __device__ static const float PI2_F = 2.0f * 3.14159265358979323846f;
 
 constexpr int ORI_WARPS = 8;
 
-__device__ __forceinline__ float gauss_at( const PyrLayout& L, int o, int lvl, int x, int y )
-{
-    x = min( max( x, 0 ), L.w[o] - 1 );
-    y = min( max( y, 0 ), L.h[o] - 1 );
-    return __ldg( L.base[o] + (size_t)lvl * L.lstride[o] + (size_t)y * L.pitch[o] + x );
-}
-
 __global__ void __launch_bounds__( ORI_WARPS * 32 )
-k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ cand, const Counters* __restrict__ ct,
+k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ cand, Counters* __restrict__ ct,
                psift_extremum* __restrict__ ext )
 {
     __shared__ float col[ORI_WARPS][ORI_NBINS][32];     /* lane-private histogram columns */
@@ -42,7 +35,12 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
     const int wid  = threadIdx.x >> 5;
     const int total = ct->ext_total;
 
-    for( int e = blockIdx.x * ORI_WARPS + wid; e < total; e += gridDim.x * ORI_WARPS ) {
+    /* keypoints are handed out one at a time per warp: their windows differ in size by 5x and more */
+    for( ;; ) {
+        int e = 0;
+        if( lane == 0 ) e = atomicAdd( &ct->ori_next, 1 );
+        e = __shfl_sync( 0xffffffffu, e, 0 );
+        if( e >= total ) break;
         int o = 0;
         while( o + 1 < L.n_oct && e >= ct->ext_ps[o + 1] ) o++;
         const Cand c = cand[e];
@@ -63,24 +61,30 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
         const int ymax = min( h - 2, (int)roundf( y ) + rad );
         const int wx = xmax - xmin + 1;
         const int hy = ymax - ymin + 1;
-        const int loops = wx * hy;
+        const int loops = ( wx > 0 && hy > 0 ) ? wx * hy : 0;
+        const int pitch = L.pitch[o];
+        const float* plane = L.base[o] + (size_t)min( max( level, 0 ), L.n_lvl - 1 ) * L.lstride[o];
+        const int wxs = max( wx, 1 );
+        const int q = 32 / wxs, r = 32 - q * wxs;                           /* (row, column) advance per 32 pixels */
+        int yy = ymin + lane / wxs, xx = xmin + lane % wxs;
 
         for( int i = lane; i < loops; i += 32 ) {
-            const int yy = i / wx + ymin;
-            const int xx = i % wx + xmin;
-            const float gx = __fsub_rn( gauss_at( L, o, level, xx + 1, yy ), gauss_at( L, o, level, xx - 1, yy ) );
-            const float gy = __fsub_rn( gauss_at( L, o, level, xx, yy + 1 ), gauss_at( L, o, level, xx, yy - 1 ) );
-            const float grad  = hypotf( gx, gy );
-            const float theta = atan2f( gy, gx );
+            /* 1 <= xx <= w-2 and 1 <= yy <= h-2: the four neighbours are inside the plane */
+            const float* p = plane + (size_t)yy * pitch + xx;
+            const float gx = __fsub_rn( __ldg( p + 1 ), __ldg( p - 1 ) );
+            const float gy = __fsub_rn( __ldg( p + pitch ), __ldg( p - pitch ) );
             const float dx = __fsub_rn( (float)xx, x );
             const float dy = __fsub_rn( (float)yy, y );
             const int sq_dist = (int)__fmaf_rn( dy, dy, __fmul_rn( dx, dx ) );
             if( sq_dist <= sq_thres ) {
+                const float grad  = hypotf( gx, gy );
+                const float theta = atan2f( gy, gx );
                 const float weight = __fmul_rn( grad, expf( __fmul_rn( (float)sq_dist, factor ) ) );
                 int bidx = (int)roundf( __fdividef( float( ORI_NBINS ) * ( theta + PI_F ), PI2_F ) );
                 bidx = ( bidx >= ORI_NBINS ) ? 0 : bidx;
                 col[wid][bidx][lane] += weight;
             }
+            yy += q; xx += r; if( xx > xmax ) { xx -= wx; yy++; }
         }
         __syncwarp();
         for( int b = lane; b < ORI_NBINS; b += 32 ) {
