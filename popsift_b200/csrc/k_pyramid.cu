@@ -171,10 +171,12 @@ k_blur_level( const __grid_constant__ BlurArgs a )
  * instructions is IEEE round-to-nearest, identical to the scalar FADD/FFMA sequence above, and the
  * tap order is unchanged, so the planes stay bit-identical (tests/test_parity_gpu.py).
  * ------------------------------------------------------------------------------------------ */
-/* Two tile shapes: BIG for planes that fill the GPU, SMALL for the deeper octaves, where more and
- * shorter blocks cut the latency of each (dependent) level. */
-struct TileBig   { static constexpr int TXv = 128, TYv = 64, VYv = 8; };
-struct TileSmall { static constexpr int TXv = 64,  TYv = 32, VYv = 4; };
+/* Two tile shapes: 128x32 for planes that fill the GPU several times over, 64x32 for the deeper
+ * octaves, where more and shorter blocks cut the latency of each (dependent) level.  Measured on
+ * B200 (profiles/): 128x64 tiles have less halo but only two blocks fit an SM, and the load /
+ * horizontal / vertical phases of so few blocks do not overlap enough. */
+struct TileMed { static constexpr int TXv = 128, TYv = 32, VYv = 8, UNR = 2; static constexpr int minb( int ) { return 3; } };
+struct TileSm  { static constexpr int TXv = 64,  TYv = 32, VYv = 4, UNR = 2; static constexpr int minb( int H ) { return H > 10 ? 3 : 4; } };
 
 __device__ __forceinline__ float2 ffma2( float2 a, float b, float2 c )
 {
@@ -205,7 +207,7 @@ __device__ __forceinline__ float2 fmul2( float2 a, float b )
 }
 
 template<int H, bool FROM_TEX, class T>
-__global__ void __launch_bounds__( NT, 2 )
+__global__ void __launch_bounds__( NT, T::minb( H ) )
 k_blur2( const __grid_constant__ BlurArgs a )
 {
     constexpr int TXv = T::TXv, TYv = T::TYv, VYv = T::VYv;
@@ -265,7 +267,7 @@ k_blur2( const __grid_constant__ BlurArgs a )
             }
         }
     } else {
-        #pragma unroll 4
+        #pragma unroll T::UNR
         for( int i = tid; i < RPn * SQ; i += NT ) {
             const int p = i / SQ, c4 = i % SQ;
             const int g0 = min( max( ty0 - H + 2 * p,     0 ), h - 1 );
@@ -345,7 +347,7 @@ k_blur2( const __grid_constant__ BlurArgs a )
 static long blur_small_max()
 {
     static long v = -1;
-    if( v < 0 ) { const char* e = getenv( "PSIFT_BLUR_SMALL_MAX" ); v = e ? atol( e ) : 1024L * 600L; }
+    if( v < 0 ) { const char* e = getenv( "PSIFT_BLUR_SMALL_MAX" ); v = e ? atol( e ) : 3000000L; }
     return v;
 }
 
@@ -370,8 +372,8 @@ static cudaError_t launch_v2t( const BlurArgs& a, cudaStream_t st )
 template<int H, bool FROM_TEX>
 static cudaError_t launch_v2( const BlurArgs& a, cudaStream_t st )
 {
-    if( (long)a.w * a.h <= blur_small_max() ) return launch_v2t<H, FROM_TEX, TileSmall>( a, st );
-    return launch_v2t<H, FROM_TEX, TileBig>( a, st );
+    if( (long)a.w * a.h <= blur_small_max() ) return launch_v2t<H, FROM_TEX, TileSm>( a, st );
+    return launch_v2t<H, FROM_TEX, TileMed>( a, st );
 }
 
 template<bool FROM_TEX>
@@ -444,18 +446,29 @@ static cudaError_t launch_blur( const BlurArgs& a, cudaStream_t st )
 /* Build every Gaussian level of every octave (reference Pyramid::build_pyramid,
  * s_pyramid_build.cu:460-596, default branch :549-577). */
 cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift,
-                            const GaussTables& T, cudaStream_t st, long long* launches )
+                            const GaussTables& T, const PyrStreams& S, long long* launches )
 {
-    const int ds_level = L.n_lvl - 3;      /* _levels - PREV_LEVEL, s_pyramid_build.cu:229 */
+    const int  ds_level = L.n_lvl - 3;      /* _levels - PREV_LEVEL, s_pyramid_build.cu:229 */
+    const bool fork = S.side[0] != nullptr;
+    bool side_used[2] = { false, false };
+    cudaError_t e;
     for( int o = 0; o < L.n_oct; o++ ) {
         for( int l = ( o == 0 ? 0 : 1 ); l < L.n_lvl; l++ ) {
+            cudaStream_t st = S.chain;
+            if( fork && l > ds_level ) {
+                st = S.side[o & 1];
+                if( l == ds_level + 1 ) {
+                    if( ( e = cudaEventRecord( S.seeded[o], S.chain ) ) != cudaSuccess ) return e;
+                    if( ( e = cudaStreamWaitEvent( st, S.seeded[o], 0 ) ) != cudaSuccess ) return e;
+                    side_used[o & 1] = true;
+                }
+            }
             BlurArgs a;
             a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
             a.dst = L.base[o] + (size_t)l * L.lstride[o];
             a.ds_dst = nullptr; a.ds_pitch = 0;
             if( l == ds_level && o + 1 < L.n_oct ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
             a.shift = shift;
-            cudaError_t e;
             if( l == 0 ) {
                 a.src = nullptr; a.tex = input_tex;
                 a.th = T.dd[0]; a.tv = T.inc[0];
@@ -469,6 +482,11 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
             if( launches ) ++*launches;
         }
     }
+    for( int k = 0; k < 2; k++ )
+        if( side_used[k] ) {
+            if( ( e = cudaEventRecord( S.side_done[k], S.side[k] ) ) != cudaSuccess ) return e;
+            if( ( e = cudaStreamWaitEvent( S.chain, S.side_done[k], 0 ) ) != cudaSuccess ) return e;
+        }
     return cudaSuccess;
 }
 

@@ -5,8 +5,18 @@
 namespace psift {
 
 /* k_pyramid.cu */
+/* Streams of one frame's pyramid build.  The dependency chain (levels 1..levels of every octave,
+ * each octave seeded by the previous one's level `levels`) runs on `chain`; the two remaining
+ * levels of each octave hang off that chain and run on side[octave & 1], so that the short,
+ * latency-bound launches of the deep octaves overlap the large ones.  side[0] == nullptr: serial. */
+struct PyrStreams {
+    cudaStream_t chain;
+    cudaStream_t side[2];
+    cudaEvent_t  seeded[MAX_OCT];    /* level `levels` of octave o is complete */
+    cudaEvent_t  side_done[2];
+};
 cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift,
-                            const GaussTables& T, cudaStream_t st, long long* launches );
+                            const GaussTables& T, const PyrStreams& S, long long* launches );
 /* k_extrema.cu */
 cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted,
                             int ext_capacity, Counters* ct, cudaStream_t st, long long* launches );

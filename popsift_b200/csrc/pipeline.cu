@@ -40,6 +40,7 @@ struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t  ev[N_EVENTS] = {};
     cudaEvent_t  ev_counters = nullptr;
+    PyrStreams   ps = {};                                   /* chain = stream, two side streams, fork/join events */
     bool         busy = false;
 
     /* input */
@@ -118,6 +119,11 @@ static void free_slot( Slot& s )
     if( s.h_desc ) cudaFreeHost( s.h_desc );
     for( auto& e : s.ev ) if( e ) cudaEventDestroy( e );
     if( s.ev_counters ) cudaEventDestroy( s.ev_counters );
+    for( auto& e : s.ps.seeded ) if( e ) cudaEventDestroy( e );
+    for( int k = 0; k < 2; k++ ) {
+        if( s.ps.side_done[k] ) cudaEventDestroy( s.ps.side_done[k] );
+        if( s.ps.side[k] ) cudaStreamDestroy( s.ps.side[k] );
+    }
     if( s.stream ) cudaStreamDestroy( s.stream );
     s = Slot();
 }
@@ -209,6 +215,14 @@ static int init_slot( psift_ctx* c, Slot& s )
     CU( cudaStreamCreateWithFlags( &s.stream, cudaStreamNonBlocking ) );
     for( auto& e : s.ev ) CU( cudaEventCreate( &e ) );
     CU( cudaEventCreateWithFlags( &s.ev_counters, cudaEventDisableTiming ) );
+    s.ps.chain = s.stream;
+    if( !getenv( "PSIFT_SERIAL_PYRAMID" ) ) {
+        for( int k = 0; k < 2; k++ ) {
+            CU( cudaStreamCreateWithFlags( &s.ps.side[k], cudaStreamNonBlocking ) );
+            CU( cudaEventCreateWithFlags( &s.ps.side_done[k], cudaEventDisableTiming ) );
+        }
+        for( auto& e : s.ps.seeded ) CU( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ) );
+    }
     const int me = c->cfg.max_extrema;
     s.cand_stride = me;
     s.ext_cap  = me;                                     /* sift_pyramid.cu:148-151 */
@@ -253,7 +267,7 @@ static int run_frame( psift_ctx* c, Slot& s )
     float shift = 0.5f;                                              /* s_pyramid_build.cu:110-114 */
     if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT )
         shift = 0.5f * powf( 2.0f, c->cfg.upscale_factor );
-    CU( launch_pyramid( L, s.img_tex, shift, c->gt, st, &c->launches ) );
+    CU( launch_pyramid( L, s.img_tex, shift, c->gt, s.ps, &c->launches ) );
     CU( cudaEventRecord( s.ev[2], st ) );
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
     CU( cudaEventRecord( s.ev[3], st ) );
