@@ -188,7 +188,7 @@ struct ExtGrid {
 };
 
 constexpr int EX_TX = 64, EX_TY = 16, EX_NT = 256;
-constexpr int EX_SW = EX_TX + 4;           /* DoG tile row: 1 halo column each side, padded to 68 */
+constexpr int EX_SW = EX_TX + 8;           /* DoG tile row: tile column x sits at x+4, so that rows load and read as float4 */
 constexpr int EX_SH = EX_TY + 2;
 
 static size_t extrema_smem( int n_lvl )
@@ -230,51 +230,64 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     DogView dv;
     dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = n_lvl;
 
-    /* ---- load: Gaussian levels -> DoG tile ---- */
-    constexpr int LW = EX_TX + 2;
-    for( int i = tid; i < EX_SH * LW; i += EX_NT ) {
-        const int sy = i / LW, sx = i % LW;
-        const int gx = min( max( tx0 - 1 + sx, 0 ), w - 1 );
-        const int gy = min( max( ty0 - 1 + sy, 0 ), h - 1 );
-        const float* p = dv.base + (size_t)gy * dv.pitch + gx;
-        float* d = D + sy * EX_SW + sx;
+    /* ---- load: Gaussian levels -> DoG tile, four columns at a time ----
+     * Tile column x is stored at x+4: shared column 3 is the left halo, EX_TX+4 the right one.
+     * Columns outside the image are never looked at (candidates keep one pixel away from the
+     * border), so a float4 that would leave the row's allocation is simply not loaded. */
+    constexpr int LQ = EX_SW / 4;
+    for( int i = tid; i < EX_SH * LQ; i += EX_NT ) {
+        const int sy = i / LQ, c4 = i % LQ;
+        const int gx0 = tx0 - 4 + 4 * c4;
+        const int gy  = min( max( ty0 - 1 + sy, 0 ), h - 1 );
+        float4* d = reinterpret_cast<float4*>( D + sy * EX_SW ) + c4;
+        const bool ok = ( gx0 >= 0 ) && ( gx0 + 3 < dv.pitch );
+        const float4* p = reinterpret_cast<const float4*>( dv.base + (size_t)gy * dv.pitch + ( ok ? gx0 : 0 ) );
+        const size_t ls4 = dv.lstride / 4;                                  /* planes are 512-byte aligned */
         if( NLVL ) {
-            float g[NLVL ? NLVL : 1];
+            float4 g[NLVL ? NLVL : 1];
             #pragma unroll
-            for( int l = 0; l < NLVL; l++ ) g[l] = __ldg( p + (size_t)l * dv.lstride );
+            for( int l = 0; l < NLVL; l++ ) g[l] = __ldg( p + l * ls4 );
             #pragma unroll
-            for( int l = 0; l + 1 < NLVL; l++ ) d[l * EX_SH * EX_SW] = __fsub_rn( g[l + 1], g[l] );
+            for( int l = 0; l + 1 < NLVL; l++ )
+                d[l * ( EX_SH * EX_SW / 4 )] = make_float4( __fsub_rn( g[l + 1].x, g[l].x ), __fsub_rn( g[l + 1].y, g[l].y ),
+                                                            __fsub_rn( g[l + 1].z, g[l].z ), __fsub_rn( g[l + 1].w, g[l].w ) );
         } else {
-            float prev = __ldg( p );
+            float4 prev = __ldg( p );
             for( int l = 1; l < n_lvl; l++ ) {
-                const float cur = __ldg( p + (size_t)l * dv.lstride );
-                d[( l - 1 ) * EX_SH * EX_SW] = __fsub_rn( cur, prev );
+                const float4 cur = __ldg( p + l * ls4 );
+                d[( l - 1 ) * ( EX_SH * EX_SW / 4 )] = make_float4( __fsub_rn( cur.x, prev.x ), __fsub_rn( cur.y, prev.y ),
+                                                                    __fsub_rn( cur.z, prev.z ), __fsub_rn( cur.w, prev.w ) );
                 prev = cur;
             }
         }
     }
     __syncthreads();
 
-    /* ---- phase 1: first contrast test ---- */
-    const int lane = tid & 31;
-    #pragma unroll
-    for( int k = 0; k < EX_TX * EX_TY / EX_NT; k++ ) {
-        const int idx = tid + k * EX_NT;
-        const int x = idx % EX_TX, y = idx / EX_TX;
-        const int gx = tx0 + x, gy = ty0 + y;
-        bool inside = ( gx >= 1 ) && ( gy >= 1 ) && ( gx <= w - 2 ) && ( gy <= h - 2 );
-        if( MODE == PSIFT_MODE_OPENCV ) inside = inside && !( gx < 5 || gy < 5 || gx >= w - 5 || gy >= h - 5 );   /* :336-340 */
-        for( int level = 1; level <= n_lvl - 3; level++ ) {
-            const float v = D[( level * EX_SH + y + 1 ) * EX_SW + x + 1];
-            const bool pass = inside && first_contrast_ok<MODE>( v, K.threshold );
-            const unsigned mask = __ballot_sync( 0xffffffffu, pass );
-            if( mask ) {
-                int base = 0;
-                if( lane == 0 ) base = atomicAdd( &n1, __popc( mask ) );
-                base = __shfl_sync( 0xffffffffu, base, 0 );
-                if( pass ) q1[base + __popc( mask & ( ( 1u << lane ) - 1 ) )] = (unsigned short)( x | ( y << 6 ) | ( level << 10 ) );
-            }
+    /* ---- phase 1: first contrast test, four voxels per thread and level ---- */
+    {
+        const int g = tid % ( EX_TX / 4 ), y = tid / ( EX_TX / 4 );       /* 16 x 16 threads = 64 x 16 pixels */
+        const int gy = ty0 + y;
+        unsigned inside = 0;
+        #pragma unroll
+        for( int j = 0; j < 4; j++ ) {
+            const int gx = tx0 + 4 * g + j;
+            bool in = ( gx >= 1 ) && ( gy >= 1 ) && ( gx <= w - 2 ) && ( gy <= h - 2 );
+            if( MODE == PSIFT_MODE_OPENCV ) in = in && !( gx < 5 || gy < 5 || gx >= w - 5 || gy >= h - 5 );   /* :336-340 */
+            inside |= in ? ( 1u << j ) : 0u;
         }
+        if( inside )
+            for( int level = 1; level <= n_lvl - 3; level++ ) {
+                const float4 v = *reinterpret_cast<const float4*>( D + ( level * EX_SH + y + 1 ) * EX_SW + 4 * g + 4 );
+                unsigned m = ( first_contrast_ok<MODE>( v.x, K.threshold ) ? 1u : 0u ) | ( first_contrast_ok<MODE>( v.y, K.threshold ) ? 2u : 0u )
+                           | ( first_contrast_ok<MODE>( v.z, K.threshold ) ? 4u : 0u ) | ( first_contrast_ok<MODE>( v.w, K.threshold ) ? 8u : 0u );
+                m &= inside;
+                if( m ) {
+                    int pos = atomicAdd( &n1, __popc( m ) );
+                    #pragma unroll
+                    for( int j = 0; j < 4; j++ )
+                        if( m & ( 1u << j ) ) q1[pos++] = (unsigned short)( ( 4 * g + j ) | ( y << 6 ) | ( level << 10 ) );
+                }
+            }
     }
     __syncthreads();
 
@@ -283,7 +296,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     for( int i = tid; i < cnt1; i += EX_NT ) {
         const unsigned e = q1[i];
         const int x = e & 63, y = ( e >> 6 ) & 15, level = e >> 10;
-        const float* c = D + ( level * EX_SH + y + 1 ) * EX_SW + x + 1;
+        const float* c = D + ( level * EX_SH + y + 1 ) * EX_SW + x + 4;
         const float v = *c;
         bool gt = true, lt = true;
         #pragma unroll
@@ -316,7 +329,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     for( int i = tid; i < cnt2; i += EX_NT ) {
         const unsigned e = q2[i];
         const int x = tx0 + ( e & 63 ), y = ty0 + ( ( e >> 6 ) & 15 ), level = e >> 10;
-        const float val = D[( level * EX_SH + ( y - ty0 ) + 1 ) * EX_SW + ( x - tx0 ) + 1];
+        const float val = D[( level * EX_SH + ( y - ty0 ) + 1 ) * EX_SW + ( x - tx0 ) + 4];
         Cand c;
         if( refine_extremum<MODE>( dv, K, x, y, level, val, w_div, h_div, c ) ) {
             c.key_lo = (uint32_t)x | ( (uint32_t)( y & 0xf ) << 28 );
