@@ -6,7 +6,7 @@ CSRC   := popsift_b200/csrc
 OBJDIR := build/obj
 LIB    := popsift_b200/libpopsift_b200.so
 
-CU_SRCS  := $(CSRC)/k_pyramid.cu $(CSRC)/k_extrema.cu $(CSRC)/k_orient.cu $(CSRC)/k_desc.cu $(CSRC)/pipeline.cu
+CU_SRCS  := $(CSRC)/k_pyramid.cu $(CSRC)/k_extrema.cu $(CSRC)/k_filter.cu $(CSRC)/k_orient.cu $(CSRC)/k_desc.cu $(CSRC)/pipeline.cu
 CPP_SRCS := $(CSRC)/tables.cpp $(wildcard $(CSRC)/host/*.cpp)
 OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU_SRCS)) $(patsubst $(CSRC)/%.cpp,$(OBJDIR)/%.o,$(CPP_SRCS))
 

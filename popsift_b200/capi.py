@@ -39,7 +39,7 @@ GAUSS = {"vlfeat": 0, "vlfeat-hw-interpolated": 1, "relative": 1, "vlfeat-direct
 MODE = {"popsift": 0, "opencv": 1, "vlfeat": 2}
 DESC = {"loop": 0, "iloop": 1, "grid": 2, "igrid": 3, "notile": 4}
 NORM = {"RootSift": 0, "classic": 1}
-FSORT = {"random": 0, "up": 1, "down": 2}
+FSORT = {"random": 0, "down": 1, "up": 2}   # reference sift_conf.cu:131-141 (up = smallest scale first)
 
 EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "psift_create", "psift_configure",
            "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_wait",

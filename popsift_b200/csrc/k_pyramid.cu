@@ -445,9 +445,13 @@ static cudaError_t launch_blur( const BlurArgs& a, cudaStream_t st )
 
 /* Build every Gaussian level of every octave (reference Pyramid::build_pyramid,
  * s_pyramid_build.cu:460-596, default branch :549-577). */
-cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift,
+cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, int gauss_mode,
                             const GaussTables& T, const PyrStreams& S, long long* launches )
 {
+    /* VLFeat_Relative_All ("vlfeat-direct"): every level of octave 0 is filtered straight from the
+     * input image with the absolute tables (horiz_all + vert_all_abs0, s_pyramid_build.cu:545-548,
+     * s_pyramid_build_ra.cu:93-129, s_pyramid_build_aa.cu:133-176); the other octaves are built as usual. */
+    const bool direct_o0 = gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE_ALL;
     const int  ds_level = L.n_lvl - 3;      /* _levels - PREV_LEVEL, s_pyramid_build.cu:229 */
     const bool fork = S.side[0] != nullptr;
     bool side_used[2] = { false, false };
@@ -469,7 +473,11 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
             a.ds_dst = nullptr; a.ds_pitch = 0;
             if( l == ds_level && o + 1 < L.n_oct ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
             a.shift = shift;
-            if( l == 0 ) {
+            if( o == 0 && direct_o0 ) {
+                a.src = nullptr; a.tex = input_tex;
+                a.th = T.abs_o0[l]; a.tv = T.abs_o0[l];
+                e = launch_blur<true>( a, st );
+            } else if( l == 0 ) {
                 a.src = nullptr; a.tex = input_tex;
                 a.th = T.dd[0]; a.tv = T.inc[0];
                 e = launch_blur<true>( a, st );

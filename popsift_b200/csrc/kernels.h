@@ -15,11 +15,15 @@ struct PyrStreams {
     cudaEvent_t  seeded[MAX_OCT];    /* level `levels` of octave o is complete */
     cudaEvent_t  side_done[2];
 };
-cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift,
+cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, int gauss_mode,
                             const GaussTables& T, const PyrStreams& S, long long* launches );
 /* k_extrema.cu */
 cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted,
                             int ext_capacity, Counters* ct, cudaStream_t st, long long* launches );
+/* k_filter.cu */
+size_t filter_scratch_bytes( int ext_capacity );
+cudaError_t launch_grid_filter( const PyrLayout& L, const psift_config& cfg, Cand* list, Cand* spare, int ext_capacity,
+                                Counters* ct, void* scratch, cudaStream_t st, long long* launches );
 /* k_orient.cu */
 cudaError_t launch_orientation( const PyrLayout& L, const Cand* sorted, Counters* ct, psift_extremum* ext,
                                 int* desc_map, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches );

@@ -64,6 +64,7 @@ struct Slot {
     int*   desc_map = nullptr;
     float* desc = nullptr;
     Counters* ct = nullptr;
+    void*  filt = nullptr;                                  /* grid filter scratch */
 
     /* host results (pinned) */
     Counters* h_ct = nullptr;
@@ -112,7 +113,7 @@ static void free_slot( Slot& s )
     if( s.img_tex ) cudaDestroyTextureObject( s.img_tex );
     if( s.d_img ) cudaFree( s.d_img );
     if( s.h_img ) cudaFreeHost( s.h_img );
-    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.ct );
+    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
     if( s.h_ct ) cudaFreeHost( s.h_ct );
     if( s.h_ext ) cudaFreeHost( s.h_ext );
     if( s.h_feat ) cudaFreeHost( s.h_feat );
@@ -234,6 +235,7 @@ static int init_slot( psift_ctx* c, Slot& s )
     CU( cudaMalloc( &s.desc_map, sizeof(int) * (size_t)s.desc_cap ) );
     CU( cudaMalloc( &s.desc,   sizeof(float) * 128 * (size_t)s.desc_cap ) );
     CU( cudaMalloc( &s.ct, sizeof(Counters) ) );
+    CU( cudaMalloc( &s.filt, filter_scratch_bytes( s.ext_cap ) ) );
     CU( cudaMallocHost( &s.h_ct, sizeof(Counters) ) );
     return PSIFT_OK;
 }
@@ -267,9 +269,10 @@ static int run_frame( psift_ctx* c, Slot& s )
     float shift = 0.5f;                                              /* s_pyramid_build.cu:110-114 */
     if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT )
         shift = 0.5f * powf( 2.0f, c->cfg.upscale_factor );
-    CU( launch_pyramid( L, s.img_tex, shift, c->gt, s.ps, &c->launches ) );
+    CU( launch_pyramid( L, s.img_tex, shift, c->cfg.gauss_mode, c->gt, s.ps, &c->launches ) );
     CU( cudaEventRecord( s.ev[2], st ) );
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
+    CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
     CU( cudaEventRecord( s.ev[3], st ) );
     CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, 148 * 5, st, &c->launches ) );
     CU( cudaEventRecord( s.ev[4], st ) );
@@ -324,15 +327,15 @@ int psift_device_count( void )
 static int check_config( const psift_config* cfg )
 {
     if( !cfg ) return fail( PSIFT_E_INVALID, "null config" );
-    if( cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_COMPUTE && cfg->gauss_mode != PSIFT_GAUSS_OPENCV_COMPUTE )
-        return fail( PSIFT_E_INVALID, "gauss mode %d not built yet (vlfeat and opencv are)", cfg->gauss_mode );
-    if( cfg->desc_mode == PSIFT_DESC_ILOOP ) return fail( PSIFT_E_INVALID, "desc mode iloop not built yet" );
+    if( cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_COMPUTE && cfg->gauss_mode != PSIFT_GAUSS_OPENCV_COMPUTE &&
+        cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE_ALL )
+        return fail( PSIFT_E_INVALID, "gauss mode %d not built yet (vlfeat, vlfeat-direct and opencv are)", cfg->gauss_mode );
     if( cfg->desc_mode < 0 || cfg->desc_mode > PSIFT_DESC_NOTILE ) return fail( PSIFT_E_INVALID, "bad desc mode" );
     if( cfg->sift_mode < 0 || cfg->sift_mode > PSIFT_MODE_VLFEAT ) return fail( PSIFT_E_INVALID, "bad sift mode" );
     if( cfg->max_extrema < 1 ) return fail( PSIFT_E_INVALID, "max_extrema must be positive" );
     if( cfg->upscale_factor != floorf( cfg->upscale_factor ) || cfg->upscale_factor > 4 || cfg->upscale_factor < -8 )
         return fail( PSIFT_E_INVALID, "downsampling must be an integer in [-4, 8]" );
-    if( cfg->filter_grid_size < 1 ) return fail( PSIFT_E_INVALID, "filter grid size must be positive" );
+    if( cfg->filter_grid_size < 1 || cfg->filter_grid_size > 32 ) return fail( PSIFT_E_INVALID, "filter grid size must be in 1..32" );
     return PSIFT_OK;
 }
 

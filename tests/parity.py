@@ -77,6 +77,25 @@ def compare(mine, ref, norm_multi=0, skip_last_desc=True):
     return rep
 
 
+def cell_histogram(ext, w0, h0, grid):
+    """Keypoints per grid-filter cell (reference s_extrema.cu: cell = floor(y/(h/g))*g + floor(x/(w/g)),
+    octave coordinates; octave o is ceil-halved o times from w0 x h0)."""
+    hist = np.zeros(grid * grid, np.int64)
+    for e in ext:
+        w, h = w0, h0
+        for _ in range(int(e["octave"])):
+            w, h = (w + 1) // 2, (h + 1) // 2
+        wd, hd = np.float32(w) / np.float32(grid), np.float32(h) / np.float32(grid)
+        hist[int(np.floor(np.float32(e["y"]) / hd)) * grid + int(np.floor(np.float32(e["x"]) / wd))] += 1
+    return hist
+
+
+def filter_params(flags):
+    g = int(flags[flags.index("--filter-grid") + 1]) if "--filter-grid" in flags else 2
+    srt = flags[flags.index("--filter-sort") + 1] if "--filter-sort" in flags else "random"
+    return g, srt
+
+
 def compare_planes(ctx, planes):
     """Gaussian and DoG planes vs the reference dump: returns (n_planes, n_bitexact, max_abs_diff)."""
     n = nb = 0

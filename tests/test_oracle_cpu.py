@@ -8,7 +8,7 @@ from tools import golden_cases as gc
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(ROOT, "oracle", "cpu_sift")
-SKIP_FLAGS = {"iloop"}                       # not restated
+SKIP_FLAGS = {"relative", "fixed9", "fixed15"}   # Gauss modes not restated
 CASES = [c for c, (_, flags, _) in gc.CASES.items()
          if os.path.exists(os.path.join(refio.GOLD, "ref", c + ".feat.bin")) and not (set(flags) & SKIP_FLAGS)]
 # bilinear float textures (igrid/notile) are blended in float on the CPU: descriptor tolerance is looser there
@@ -35,6 +35,13 @@ def test_oracle_matches_reference_cuda_output(tmp_path, case):
     mine, ref = refio.RefFeatures(out + ".feat.bin"), refio.RefFeatures(os.path.join(refio.GOLD, "ref", case + ".feat.bin"))
     flags = gc.CASES[case][1]
     nm = int(flags[flags.index("--norm-multi") + 1]) if "--norm-multi" in flags else 0
+    if "--filter-max-extrema" in flags and parity.filter_params(flags)[1] == "random":
+        # which keypoints of a cell survive depends on the reference's atomic arrival order: only the
+        # number kept per octave and per cell is defined
+        g = parity.filter_params(flags)[0]
+        assert mine.n_feat == ref.n_feat and np.array_equal(mine.ext_ct, ref.ext_ct)
+        assert np.array_equal(parity.cell_histogram(mine.ext, mine.w0, mine.h0, g), parity.cell_histogram(ref.ext, ref.w0, ref.h0, g))
+        return
     rep = parity.compare(mine, ref, norm_multi=nm)
     assert rep["ok_int"], rep                         # counts, octave, level, num_ori
     assert rep["xy_bitexact"], rep                    # refinement is +,-,*,fma,1/x only: exact on the CPU too

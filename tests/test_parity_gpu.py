@@ -39,6 +39,13 @@ def test_features_match_reference_golden(case):
     with ctx:
         mine = ctx.extract(load(img))
         ref = refio.RefFeatures(os.path.join(refio.GOLD, "ref", case + ".feat.bin"))
+        if "--filter-max-extrema" in flags and parity.filter_params(flags)[1] == "random":
+            # which keypoints of a cell survive depends on the reference's atomic arrival order: only
+            # the number kept per octave and per cell is defined
+            g = parity.filter_params(flags)[0]
+            assert mine.n_feat == ref.n_feat and np.array_equal(np.asarray(mine.ext_ct)[:9], ref.ext_ct[:9])
+            assert np.array_equal(parity.cell_histogram(mine.ext, ref.w0, ref.h0, g), parity.cell_histogram(ref.ext, ref.w0, ref.h0, g))
+            return
         rep = parity.compare(mine, ref, norm_multi=cfg.norm_multi)
         assert rep["ok_int"], rep                      # counts, octave, level, num_ori: bit-exact
         assert rep["xy_bitexact"] and rep["sigma_bitexact"], rep
@@ -177,7 +184,11 @@ def test_cpp_api_demo_matches_golden(tmp_path):
 ORACLE = os.path.join(ROOT, "oracle", "cpu_sift")
 ORACLE_CASES = [(200, 150, 21, []), (97, 131, 22, []), (320, 240, 23, ["--mode", "vlfeat", "--desc-mode", "grid"]),
                 (161, 243, 24, ["--downsampling", "0", "--norm-mode", "classic"]), (128, 128, 25, ["--mode", "opencv", "--gauss-mode", "opencv"]),
-                (300, 200, 26, ["--levels", "5"]), (64, 256, 27, ["--sigma", "1.2", "--threshold", "0.02", "--edge-threshold", "8"])]
+                (300, 200, 26, ["--levels", "5"]), (64, 256, 27, ["--sigma", "1.2", "--threshold", "0.02", "--edge-threshold", "8"]),
+                (400, 300, 28, ["--filter-max-extrema", "120", "--filter-grid", "4", "--filter-sort", "down"]),
+                (400, 300, 29, ["--filter-max-extrema", "90", "--filter-grid", "3", "--filter-sort", "up"]),
+                (400, 300, 30, ["--filter-max-extrema", "100", "--filter-grid", "5", "--filter-sort", "random"]),
+                (256, 192, 31, ["--desc-mode", "iloop"]), (192, 256, 32, ["--gauss-mode", "vlfeat-direct"])]
 
 
 @pytest.mark.skipif(not os.path.exists(ORACLE), reason="oracle/cpu_sift not built")
@@ -197,4 +208,5 @@ def test_cuda_path_against_cpu_oracle(tmp_path, w, h, seed, flags):
     assert n == nb, (n, nb, mx)                       # every Gaussian and DoG plane bit-exact
     assert rep["ok_int"] and rep["xy_bitexact"], rep
     assert rep["max_dsigma_rel"] < 1e-6 and rep["max_dtheta"] < parity.TOL_THETA, rep
-    assert rep["max_desc_l2"] < (0.05 if "grid" in flags else parity.TOL_DESC), rep
+    # grid rounds sample positions; iloop samples through the bilinear unit, blended in float on the CPU
+    assert rep["max_desc_l2"] < (0.05 if "grid" in flags else 2e-2 if "iloop" in flags else parity.TOL_DESC), rep

@@ -45,9 +45,17 @@ CASES = {
     "g256_down0":       ("g256",   ["--downsampling", "0"], False),
     "g256_down1":       ("g256",   ["--downsampling", "1"], False),
     "g256_levels4":     ("g256",   ["--levels", "4"], False),
-    "g256_filter":      ("g256",   ["--filter-max-extrema", "200", "--filter-grid", "4", "--filter-sort", "down"], False),
-    "g256_filter_up":   ("g256",   ["--filter-max-extrema", "200", "--filter-grid", "2", "--filter-sort", "up"], False),
+    "g256_filter":      ("g256",   ["--filter-max-extrema", "40", "--filter-grid", "4", "--filter-sort", "down"], False),
+    "g256_filter_up":   ("g256",   ["--filter-max-extrema", "40", "--filter-grid", "2", "--filter-sort", "up"], False),
+    "g640_filter":      ("g640",   ["--filter-max-extrema", "200", "--filter-grid", "4", "--filter-sort", "down"], False),
+    "g640_filter_up":   ("g640",   ["--filter-max-extrema", "120", "--filter-grid", "3", "--filter-sort", "up"], False),
+    "g640_filter_rand": ("g640",   ["--filter-max-extrema", "150", "--filter-grid", "3", "--filter-sort", "random"], False),
     "g640_default":     ("g640",   [], False),
+    "g64_direct":       ("g64",    ["--gauss-mode", "vlfeat-direct"], True),
+    "g256_direct":      ("g256",   ["--gauss-mode", "vlfeat-direct"], False),
+    "g64_relative":     ("g64",    ["--gauss-mode", "relative"], True),
+    "g64_fixed9":       ("g64",    ["--gauss-mode", "fixed9"], True),
+    "g64_fixed15":      ("g64",    ["--gauss-mode", "fixed15"], True),
 }
 
 
