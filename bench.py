@@ -10,7 +10,7 @@ line on rank 0.  Workload = BASELINE.json configs[3]/[1] (1080p frames through e
   value     images/s over all GPUs, inputs already resident in HBM (psift_submit_dev_u8), results
             downloaded to pinned host memory (the download is part of the path).
   e2e       the same through psift_submit_u8 with HOST buffers: private host copy + H2D inside.
-  roofline  pyramid stage (all k_blur_level launches of a frame): algorithmic bytes
+  roofline  pyramid stage (all k_blur2 launches of a frame): algorithmic bytes
             A_pyr = w*h + 4*L*sum(octave pixels) over the CUDA-event time of the stage.
   cpu_baseline  the CPU restatement (oracle/) timed on one host core on ONE frame -- the
             reference has no CPU SIFT path at all, so this is a port, not the reference.
@@ -40,22 +40,49 @@ def pyramid_bytes(cfg_levels=3, up=1):
 
 
 class ClockSampler:
-    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons during the timed region (B200_PROFILING.md's clocks line), read
+    through NVML in-process.  Spawning nvidia-smi five times a second instead takes driver locks
+    often enough to slow the reference arm, which synchronises the device many times per frame,
+    by 3x (measured) -- that would flatter the comparison, so it is only the fallback, once a second."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    BITS = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
 
     def __init__(self, index):
         self.index, self.samples, self.stop = index, [], False
         self.t = threading.Thread(target=self.run, daemon=True)
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def sample(self):
+        if self.nvml:
+            n = self.nvml
+            sm = n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)
+            mx = n.nvmlDeviceGetMaxClockInfo(self.h, n.NVML_CLOCK_SM)
+            try:
+                r = n.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:
+                r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            return [str(sm), str(mx)] + ["Active" if r & self.BITS[k] else "Not Active" for k in ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")]
+        o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                           capture_output=True, text=True, timeout=5).stdout.strip()
+        return [x.strip() for x in o.split(",")] if o else None
 
     def run(self):
         while not self.stop:
             try:
-                o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                   capture_output=True, text=True, timeout=5).stdout.strip()
-                if o: self.samples.append([x.strip() for x in o.split(",")])
+                v = self.sample()
+                if v: self.samples.append(v)
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.1 if self.nvml else 1.0)
 
     def __enter__(self): self.t.start(); return self
     def __exit__(self, *a): self.stop = True; self.t.join(timeout=6)
@@ -68,7 +95,7 @@ class ClockSampler:
             for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], s[2:6]):
                 if v.lower().startswith("active"): reasons.add(name)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(self.samples)}
+                "reasons": sorted(reasons), "samples": len(self.samples), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 def frames():
@@ -130,8 +157,9 @@ def bench_reference(args, rank):
                             "frames_per_step": BATCH, "distinct_frames": N_DISTINCT,
                             "note": "the reference's own CUDA kernels built for sm_100 (two sm_70+ hazards fixed in a build-tree copy, oracle/Makefile.ref), driven like its worker thread: load -> step1 -> step2 -> get_descriptors, one image at a time; single GPU only"},
                  "features_per_frame": d["features_total"] / max(d["iters"], 1),
-                 "cpu_baseline": {"value": None, "unit": "images/s", "cores": 0, "kind": "reference", "sample": "the reference has no CPU implementation; this arm is its CUDA build on the same B200"},
-                 "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": W * H * BATCH, "d2h_bytes_per_step": None},
+                 "cpu_baseline": {"value": v, "unit": "images/s", "cores": 1, "kind": "reference",
+                                  "sample": "%d frames 1920x1080; the reference has NO CPU implementation of this path, so this arm is its own CUDA build on the same B200, driven by one host thread" % (args.steps * BATCH)},
+                 "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": None, "clocks": cs.summary()})
     print(json.dumps(base))
 
@@ -169,22 +197,27 @@ def main():
     sub_host = lambda im: ctx.submit(im)
 
     def timed(submit, src):
+        """K steps: device time between two CUDA-event marks that join every stream of the context
+        (psift_debug_mark), max over ranks; the wall clock around the same region is kept as a check."""
         for _ in range(args.warmup): run_stream(ctx, submit, src, BATCH)
-        barrier()
+        torch.cuda.synchronize(); barrier(); torch.cuda.synchronize()
+        ctx.mark(0)
         t0 = time.perf_counter()
         nf = nd = 0
         for _ in range(args.steps):
             a, b = run_stream(ctx, submit, src, BATCH); nf += a; nd += b
-        barrier()
-        dt = time.perf_counter() - t0
-        dt = pdist.max_over_ranks(dt)
-        return dt, pdist.sum_over_ranks(nf) / world, pdist.sum_over_ranks(nd) / world
+        ctx.mark(1)
+        dt = ctx.mark_elapsed_ms() * 1e-3
+        torch.cuda.synchronize(); barrier(); torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        dt = pdist.max_over_ranks(dt); wall = pdist.max_over_ranks(wall)
+        return dt, pdist.sum_over_ranks(nf) / world, pdist.sum_over_ranks(nd) / world, wall
 
     l0 = ctx.launch_count()
     with ClockSampler(local) as cs:
-        dt_dev, nf, nd = timed(sub_dev, dev_imgs)
+        dt_dev, nf, nd, wall_dev = timed(sub_dev, dev_imgs)
     launches = (ctx.launch_count() - l0) * args.steps // (args.steps + args.warmup)
-    dt_e2e, nf2, nd2 = timed(sub_host, imgs)
+    dt_e2e, nf2, nd2, wall_e2e = timed(sub_host, imgs)
     n_frames = args.steps * BATCH
 
     # kernel-stage times (CUDA events on the frame's stream), one frame at a time, warm
@@ -202,19 +235,19 @@ def main():
     if rank == 0:
         line = {"metric": "images_per_sec_1080p", "value": world * n_frames / dt_dev, "unit": "images/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt_dev / args.steps,
-                "ms_per_frame": 1e3 * dt_dev / n_frames, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_frame": 1e3 * dt_dev / n_frames, "wall_ms_per_step": 1e3 * wall_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "stream of 1920x1080 u8 frames, default popsift::Config (2x upscale -> 3840x2160 octave 0, %d octaves, 6 Gaussian levels, loop descriptors, RootSift)" % n_oct,
                            "frames_per_step": BATCH, "distinct_frames": N_DISTINCT, "in_flight": IN_FLIGHT,
                            "l2": "no explicit flush: each frame writes a %.0f MB pyramid, larger than the 126 MB L2" % (4 * 6 * sum_px / 1e6),
-                           "timing": "wall clock between device synchronisations around K steps (max over ranks); stage times from CUDA events on the frame's stream",
+                           "timing": "CUDA events joining all of the context's streams around the K steps (max over ranks); wall clock of the same region in wall_ms_per_step; stage times from CUDA events on the frame's stream",
                            "features_per_frame": nf / n_frames, "descriptors_per_frame": nd / n_frames},
-                "e2e": {"value": world * n_frames / dt_e2e, "unit": "images/s", "h2d_bytes_per_step": W * H * BATCH,
+                "e2e": {"value": world * n_frames / dt_e2e, "unit": "images/s", "wall_value": world * n_frames / wall_e2e, "h2d_bytes_per_step": W * H * BATCH,
                         "d2h_bytes_per_step": int((nf2 * (52 + 44) + nd2 * 512) / args.steps)},
                 "gpu_launches": int(launches),
                 "stage_ms": stage,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "kernel": "k_blur_level (pyramid stage, %d launches per frame)" % (n_oct * 5 + 1),
+                             "traffic": None, "kernel": "k_blur2 (pyramid stage: %d launches per frame, three streams)" % (n_oct * 5 + 1),
                              "algorithmic_bytes": a_pyr, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
                 "cpu_baseline": cpu_baseline() if not args.no_cpu else {"value": None, "unit": "images/s", "cores": 1, "kind": "port", "sample": "skipped (--no-cpu)"},
                 "clocks": cs.summary()}

@@ -137,6 +137,11 @@ int  psift_pyramid_geometry( const psift_config* cfg, int w, int h, int* w0, int
 int  psift_last_timing( psift_ctx* ctx, float ms[8] );
 /* number of kernels this library launched since the context was created */
 long long psift_launch_count( psift_ctx* ctx );
+/* Device-side stopwatch over everything queued on the context between two marks: mark 0 is
+ * stamped once all work queued so far has finished, mark 1 likewise; elapsed() waits for mark 1
+ * and returns the CUDA-event time between them.  bench.py times its K steps with it. */
+int  psift_debug_mark( psift_ctx* ctx, int which );
+int  psift_debug_mark_elapsed( psift_ctx* ctx, float* ms );
 
 #ifdef __cplusplus
 }

@@ -45,7 +45,7 @@ EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "ps
            "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_wait",
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
-           "psift_launch_count"]
+           "psift_launch_count", "psift_debug_mark", "psift_debug_mark_elapsed"]
 
 _lib = None
 
@@ -74,6 +74,8 @@ def lib():
         L.psift_debug_desc_tables.argtypes = [C.POINTER(Config), C.c_void_p, C.c_void_p, C.c_void_p]
         L.psift_pyramid_geometry.argtypes = [C.POINTER(Config), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.psift_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        L.psift_debug_mark.argtypes = [C.c_void_p, C.c_int]
+        L.psift_debug_mark_elapsed.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         _lib = L
     return _lib
 
@@ -202,6 +204,15 @@ class Context:
         ms = (C.c_float * 8)()
         _chk(lib().psift_last_timing(self._h, ms))
         return dict(zip(["upload", "pyramid", "extrema", "orientation", "descriptor", "download", "total"], [float(x) for x in ms[:7]]))
+
+    def mark(self, which):
+        """device-side stopwatch (psift_debug_mark): 0 = start, 1 = stop"""
+        _chk(lib().psift_debug_mark(self._h, which))
+
+    def mark_elapsed_ms(self):
+        ms = C.c_float()
+        _chk(lib().psift_debug_mark_elapsed(self._h, C.byref(ms)))
+        return float(ms.value)
 
     def launch_count(self):
         return int(lib().psift_launch_count(self._h))

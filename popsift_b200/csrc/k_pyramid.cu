@@ -174,7 +174,11 @@ k_blur_level( const __grid_constant__ BlurArgs a )
 /* Two tile shapes: 128x32 for planes that fill the GPU several times over, 64x32 for the deeper
  * octaves, where more and shorter blocks cut the latency of each (dependent) level.  Measured on
  * B200 (profiles/): 128x64 tiles have less halo but only two blocks fit an SM, and the load /
- * horizontal / vertical phases of so few blocks do not overlap enough. */
+ * horizontal / vertical phases of so few blocks do not overlap enough.  Two persistent variants
+ * were built and measured as well - cp.async double buffering of a row-major tile (scalar
+ * horizontal pass), and prefetching the next tile into registers - and both lost to plain
+ * one-tile blocks (25.5 and 26.8 us against 23.3 us for the 11-tap level of a 3840x2160 plane):
+ * the hardware block scheduler already overlaps the phases of three resident blocks. */
 struct TileMed { static constexpr int TXv = 128, TYv = 32, VYv = 8, UNR = 2; static constexpr int minb( int ) { return 3; } };
 struct TileSm  { static constexpr int TXv = 64,  TYv = 32, VYv = 4, UNR = 2; static constexpr int minb( int H ) { return H > 10 ? 3 : 4; } };
 
@@ -325,6 +329,10 @@ k_blur2( const __grid_constant__ BlurArgs a )
         float2 win[VYv + 2 * H];
         #pragma unroll
         for( int k = 0; k < VYv + 2 * H; k++ ) win[k] = *reinterpret_cast<const float2*>( I + ( y0 + k ) * TXv + 2 * cp );
+        const int   nval = min( VYv, h - ( ty0 + y0 ) );
+        const bool  pair = gx + 1 < w;
+        float*      row0 = a.dst + (size_t)( ty0 + y0 ) * a.pitch + gx;
+        float*      ds0  = a.ds_dst ? a.ds_dst + (size_t)( ( ty0 + y0 ) >> 1 ) * a.ds_pitch + ( gx >> 1 ) : nullptr;
         #pragma unroll
         for( int j = 0; j < VYv; j++ ) {
             float2 acc = make_float2( 0.0f, 0.0f );
@@ -334,11 +342,11 @@ k_blur2( const __grid_constant__ BlurArgs a )
                 acc = ffma2( win[H + j + off], a.tv.g[off], acc );
             }
             acc = ffma2( win[H + j], a.tv.g[0], acc );
-            const int gy = ty0 + y0 + j;
-            if( gy < h ) {
-                float* row = a.dst + (size_t)gy * a.pitch + gx;
-                if( gx + 1 < w ) *reinterpret_cast<float2*>( row ) = acc; else row[0] = acc.x;
-                if( a.ds_dst && !( gy & 1 ) ) a.ds_dst[(size_t)( gy >> 1 ) * a.ds_pitch + ( gx >> 1 )] = acc.x;
+            /* ty0 and y0 are even, so row parity is j's: the downscale rows are known at compile time */
+            if( j < nval ) {
+                float* row = row0 + (size_t)j * a.pitch;
+                if( pair ) *reinterpret_cast<float2*>( row ) = acc; else row[0] = acc.x;
+                if( ( j & 1 ) == 0 && ds0 ) ds0[(size_t)( j >> 1 ) * a.ds_pitch] = acc.x;
             }
         }
     }

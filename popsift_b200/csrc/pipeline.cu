@@ -86,6 +86,9 @@ struct psift_ctx {
     long long launches = 0;
     float last_ms[8] = { 0 };
     int last_slot = -1;
+    cudaStream_t mark_stream = nullptr;                     /* psift_debug_mark */
+    cudaEvent_t  mark_ev[2] = { nullptr, nullptr };
+    std::vector<cudaEvent_t> mark_join;
     std::mutex mu;
 };
 
@@ -437,6 +440,9 @@ void psift_destroy( psift_ctx* c )
     cudaSetDevice( c->device );
     for( auto& s : c->slots ) { if( s.stream ) cudaStreamSynchronize( s.stream ); free_slot( s ); }
     if( c->d_dt ) cudaFree( c->d_dt );
+    for( auto e : c->mark_join ) cudaEventDestroy( e );
+    for( auto e : c->mark_ev ) if( e ) cudaEventDestroy( e );
+    if( c->mark_stream ) cudaStreamDestroy( c->mark_stream );
     delete c;
 }
 
@@ -591,5 +597,32 @@ int psift_last_timing( psift_ctx* c, float ms[8] )
 }
 
 long long psift_launch_count( psift_ctx* c ) { return c ? c->launches : 0; }
+
+int psift_debug_mark( psift_ctx* c, int which )
+{
+    if( !c || which < 0 || which > 1 ) return fail( PSIFT_E_INVALID, "bad mark" );
+    std::lock_guard<std::mutex> lk( c->mu );
+    CU( cudaSetDevice( c->device ) );
+    if( !c->mark_stream ) {
+        CU( cudaStreamCreateWithFlags( &c->mark_stream, cudaStreamNonBlocking ) );
+        for( auto& e : c->mark_ev ) CU( cudaEventCreate( &e ) );
+        c->mark_join.resize( c->slots.size(), nullptr );
+        for( auto& e : c->mark_join ) CU( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ) );
+    }
+    for( size_t i = 0; i < c->slots.size(); i++ ) {
+        CU( cudaEventRecord( c->mark_join[i], c->slots[i].stream ) );
+        CU( cudaStreamWaitEvent( c->mark_stream, c->mark_join[i], 0 ) );
+    }
+    CU( cudaEventRecord( c->mark_ev[which], c->mark_stream ) );
+    return PSIFT_OK;
+}
+
+int psift_debug_mark_elapsed( psift_ctx* c, float* ms )
+{
+    if( !c || !ms || !c->mark_stream ) return fail( PSIFT_E_INVALID, "no marks set" );
+    CU( cudaEventSynchronize( c->mark_ev[1] ) );
+    CU( cudaEventElapsedTime( ms, c->mark_ev[0], c->mark_ev[1] ) );
+    return PSIFT_OK;
+}
 
 } // extern "C"
