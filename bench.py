@@ -26,6 +26,7 @@ W, H = 1920, 1080
 BATCH = 25            # frames per step per GPU
 N_DISTINCT = 16       # distinct synthetic frames cycled through (seeds 1000..1015)
 IN_FLIGHT = 4
+PYRAMID_DRAM_BYTES = 229.1e6   # measured once per round with ncu (profiles/r01b_ncu_frame_summary.txt), per frame like algorithmic_bytes
 
 
 def pyramid_bytes(cfg_levels=3, up=1):
@@ -247,7 +248,8 @@ def main():
                 "gpu_launches": int(launches),
                 "stage_ms": stage,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "kernel": "k_blur2 (pyramid stage: %d launches per frame, three streams)" % (n_oct * 5 + 1),
+                             "traffic": PYRAMID_DRAM_BYTES, "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum over the 46 k_blur2 launches of one frame, ncu --set full, profiles/r01b_ncu_frame_summary.txt",
+                             "kernel": "k_blur2 (pyramid stage: %d launches per frame, three streams)" % (n_oct * 5 + 1),
                              "algorithmic_bytes": a_pyr, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
                 "cpu_baseline": cpu_baseline() if not args.no_cpu else {"value": None, "unit": "images/s", "cores": 1, "kind": "port", "sample": "skipped (--no-cpu)"},
                 "clocks": cs.summary()}

@@ -240,10 +240,31 @@ k_blur2( const __grid_constant__ BlurArgs a )
     const int SWn  = 2 * HX + 4 * ng;
 
     /* ---- stage (clamp to edge) ---- */
-    if( FROM_TEX || tx0 - HX < 0 || tx0 + TXv + HX > w ) {
+    if( FROM_TEX ) {
+        /* one fetch per staged pixel.  A warp owns row pairs, its lanes the columns: the normalised
+         * x coordinates (one true division each, like the reference's (x + shift) / w) are computed
+         * once per thread and reused for every row pair, the y coordinates once per row pair. */
         float2* S2 = reinterpret_cast<float2*>( smem );
         const float fw = (float)w, fh = (float)h;
-        /* four independent fetches in flight per thread before the first store */
+        constexpr int NC = ( SW + 31 ) / 32;
+        const int lane = tid & 31, wid = tid >> 5;
+        float rx[NC];
+        #pragma unroll
+        for( int k = 0; k < NC; k++ ) rx[k] = __fdiv_rn( (float)( tx0 - HX + lane + 32 * k ) + a.shift, fw );   /* x unclamped: see k_blur_level */
+        for( int p = wid; p < RPn; p += NT / 32 ) {
+            const int g0 = min( max( ty0 - H + 2 * p,     0 ), h - 1 );
+            const int g1 = min( max( ty0 - H + 2 * p + 1, 0 ), h - 1 );
+            const float ry0 = __fdiv_rn( (float)g0 + a.shift, fh ), ry1 = __fdiv_rn( (float)g1 + a.shift, fh );
+            #pragma unroll
+            for( int k = 0; k < NC; k++ ) {
+                const int c = lane + 32 * k, ch = c >> 1;
+                if( c < SWn )
+                    S2[( p * 2 * SQ + ( ch & 1 ) * SQ + ( ch >> 1 ) ) * 2 + ( c & 1 )] = make_float2( tex2D<float>( a.tex, rx[k], ry0 ), tex2D<float>( a.tex, rx[k], ry1 ) );
+            }
+        }
+    } else if( tx0 - HX < 0 || tx0 + TXv + HX > w ) {
+        float2* S2 = reinterpret_cast<float2*>( smem );
+        /* four independent loads in flight per thread before the first store */
         for( int i0 = tid; i0 < RPn * SW; i0 += 4 * NT ) {
             float2 v[4];
             #pragma unroll
@@ -252,15 +273,8 @@ k_blur2( const __grid_constant__ BlurArgs a )
                 const int p = i / SW, c = i % SW;
                 const int g0 = min( max( ty0 - H + 2 * p,     0 ), h - 1 );
                 const int g1 = min( max( ty0 - H + 2 * p + 1, 0 ), h - 1 );
-                if( FROM_TEX ) {
-                    const int gx = tx0 - HX + c;                        /* x unclamped: see k_blur_level */
-                    const float rx = __fdiv_rn( (float)gx + a.shift, fw );
-                    v[u] = make_float2( tex2D<float>( a.tex, rx, __fdiv_rn( (float)g0 + a.shift, fh ) ),
-                                        tex2D<float>( a.tex, rx, __fdiv_rn( (float)g1 + a.shift, fh ) ) );
-                } else {
-                    const int gx = min( max( tx0 - HX + c, 0 ), w - 1 );
-                    v[u] = make_float2( __ldg( a.src + (size_t)g0 * a.pitch + gx ), __ldg( a.src + (size_t)g1 * a.pitch + gx ) );
-                }
+                const int gx = min( max( tx0 - HX + c, 0 ), w - 1 );
+                v[u] = make_float2( __ldg( a.src + (size_t)g0 * a.pitch + gx ), __ldg( a.src + (size_t)g1 * a.pitch + gx ) );
             }
             #pragma unroll
             for( int u = 0; u < 4; u++ ) {
