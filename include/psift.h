@@ -137,6 +137,28 @@ int  psift_pyramid_geometry( const psift_config* cfg, int w, int h, int* w0, int
 int  psift_last_timing( psift_ctx* ctx, float ms[8] );
 /* number of kernels this library launched since the context was created */
 long long psift_launch_count( psift_ctx* ctx );
+/* ---- one giant image over several GPUs (the reference has no such mode: it runs
+ * config 5 un-tiled on one GPU, sift_pyramid.cu:108-165) -------------------------------------------
+ * The image is cut into row bands, one per context (GPU).  Every context gets the WHOLE u8 image (it is
+ * the float pyramid that does not fit or takes the time, not the bytes) and builds octaves 0..split for
+ * its band plus a halo wide enough that everything the band owns is computed from exactly the data the
+ * un-split run uses; all coordinates stay global, so the results are bit-identical and the union over
+ * the bands is the un-split keypoint set.  The fused downscale leaves each context its rows of level 0 of
+ * octave split+1 (psift_band_seed); the caller gathers those rows into one plane (the ONE exchange step:
+ * all-gather over NVLink) and every context finishes the small octaves from it with
+ * psift_submit_seed_dev_f32, keeping the keypoints whose detection row falls in its band.
+ * psift_band_plan: split octave and band boundaries (rows of octave 0, bounds[parts+1]).  */
+int  psift_band_plan( const psift_config* cfg, int w, int h, int parts, int max_seed_pixels, int* split_octave, int* bounds );
+int  psift_submit_band_u8( psift_ctx* ctx, int w, int h, const uint8_t* img, size_t pitch, int on_device,
+                           int y0, int y1, int split_octave, psift_job** out );
+/* rows [row_lo,row_hi) of level 0 of octave split+1 (size seed_w x seed_h), device memory of the job's slot */
+int  psift_band_seed( psift_job* job, const float** dev_rows, int* pitch_floats, int* row_lo, int* row_hi, int* seed_w, int* seed_h );
+/* copy seed rows [row_from,row_to) to dst (device memory, row row_from first); waits for the job's stream */
+int  psift_band_seed_copy( psift_job* job, float* dst_dev, size_t dst_pitch_bytes, int row_from, int row_to );
+/* octaves first_octave.. of a w x h image from the given level-0 plane of octave first_octave */
+int  psift_submit_seed_dev_f32( psift_ctx* ctx, int w, int h, int first_octave, const float* dev_plane, size_t pitch_bytes,
+                                int y0, int y1, psift_job** out );
+
 /* Device-side stopwatch over everything queued on the context between two marks: mark 0 is
  * stamped once all work queued so far has finished, mark 1 likewise; elapsed() waits for mark 1
  * and returns the CUDA-event time between them.  bench.py times its K steps with it. */

@@ -45,7 +45,8 @@ EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "ps
            "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_wait",
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
-           "psift_launch_count", "psift_debug_mark", "psift_debug_mark_elapsed"]
+           "psift_launch_count", "psift_debug_mark", "psift_debug_mark_elapsed",
+           "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32"]
 
 _lib = None
 
@@ -74,6 +75,11 @@ def lib():
         L.psift_debug_desc_tables.argtypes = [C.POINTER(Config), C.c_void_p, C.c_void_p, C.c_void_p]
         L.psift_pyramid_geometry.argtypes = [C.POINTER(Config), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.psift_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        L.psift_band_plan.argtypes = [C.POINTER(Config), C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.psift_submit_band_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.psift_band_seed.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.psift_band_seed_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int]
+        L.psift_submit_seed_dev_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.psift_debug_mark.argtypes = [C.c_void_p, C.c_int]
         L.psift_debug_mark_elapsed.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         _lib = L
@@ -171,6 +177,30 @@ class Context:
         _chk(lib().psift_submit_dev_u8(self._h, w, h, C.c_void_p(ptr), pitch, C.byref(job)))
         return job
 
+    # ---- one giant image in row bands (psift.h, "one giant image over several GPUs") ----
+    def submit_band(self, img, y0, y1, split, w=None, h=None, pitch=None):
+        """img: host uint8 array (whole image) or a device pointer (then give w, h, pitch)"""
+        job = C.c_void_p()
+        if isinstance(img, np.ndarray):
+            img = np.ascontiguousarray(img); hh, ww = img.shape
+            _chk(lib().psift_submit_band_u8(self._h, ww, hh, img.ctypes.data, ww, 0, y0, y1, split, C.byref(job)))
+        else:
+            _chk(lib().psift_submit_band_u8(self._h, w, h, C.c_void_p(img), pitch, 1, y0, y1, split, C.byref(job)))
+        return job
+
+    def band_seed(self, job):
+        p = C.c_void_p(); pitch, lo, hi, sw, sh = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _chk(lib().psift_band_seed(job, C.byref(p), C.byref(pitch), C.byref(lo), C.byref(hi), C.byref(sw), C.byref(sh)))
+        return p.value, pitch.value, lo.value, hi.value, sw.value, sh.value
+
+    def band_seed_copy(self, job, dst_ptr, dst_pitch_bytes, row_from, row_to):
+        _chk(lib().psift_band_seed_copy(job, C.c_void_p(dst_ptr), dst_pitch_bytes, row_from, row_to))
+
+    def submit_seed(self, w, h, first_octave, plane_ptr, pitch_bytes, y0, y1):
+        job = C.c_void_p()
+        _chk(lib().psift_submit_seed_dev_f32(self._h, w, h, first_octave, C.c_void_p(plane_ptr), pitch_bytes, y0, y1, C.byref(job)))
+        return job
+
     def wait(self, job, copy=True):
         r = Result()
         _chk(lib().psift_wait(job, C.byref(r)))
@@ -228,6 +258,13 @@ def desc_tables(cfg):
     g = np.zeros((40, 40), np.float32); t = np.zeros(16, np.float32); sc = np.zeros(2, np.float32)
     _chk(lib().psift_debug_desc_tables(C.byref(cfg), g.ctypes.data, t.ctypes.data, sc.ctypes.data))
     return g, t, sc
+
+
+def band_plan(cfg, w, h, parts, max_seed_pixels=0):
+    """(split octave, [parts+1 band boundaries in rows of octave 0])"""
+    split = C.c_int(); b = (C.c_int * (parts + 1))()
+    _chk(lib().psift_band_plan(C.byref(cfg), w, h, parts, max_seed_pixels, C.byref(split), b))
+    return split.value, [int(v) for v in b]
 
 
 def geometry(cfg, w, h):

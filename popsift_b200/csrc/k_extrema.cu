@@ -23,12 +23,13 @@ struct DogView {
     const float* base;
     size_t       lstride;
     int          pitch, w, h, nlvl;      /* nlvl = number of Gaussian levels */
+    int          y_lo, y_hi;             /* stored rows (the whole plane unless banded): reads stay inside them */
     /* DoG level z at (x,y), clamp-to-edge in x,y and clamp of the layer index like the
      * reference's layered point texture (sift_octave.cu:231-248, common/assist.h:66-75) */
     __device__ __forceinline__ float at( int x, int y, int z ) const
     {
         x = min( max( x, 0 ), w - 1 );
-        y = min( max( y, 0 ), h - 1 );
+        y = min( max( y, y_lo ), y_hi - 1 );      /* y_lo = 0, y_hi = h: the reference's clamp */
         z = min( max( z, 0 ), nlvl - 2 );
         const float* p = base + (size_t)z * lstride + (size_t)y * pitch + x;
         return __fsub_rn( __ldg( p + lstride ), __ldg( p ) );
@@ -223,12 +224,13 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     const int tile = blockIdx.x - G.first_block[o];
     const int w = L.w[o], h = L.h[o];
     const int tx0 = ( tile % G.tiles_x[o] ) * EX_TX;
-    const int ty0 = ( tile / G.tiles_x[o] ) * EX_TY;
+    const int ty0 = L.row_lo[o] + ( tile / G.tiles_x[o] ) * EX_TY;
     const int tid = threadIdx.x;
     if( tid == 0 ) { n1 = 0; n2 = 0; }
 
     DogView dv;
     dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = n_lvl;
+    dv.y_lo = L.row_lo[o]; dv.y_hi = L.row_hi[o];
 
     /* ---- load: Gaussian levels -> DoG tile, four columns at a time ----
      * Tile column x is stored at x+4: shared column 3 is the left halo, EX_TX+4 the right one.
@@ -238,7 +240,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     for( int i = tid; i < EX_SH * LQ; i += EX_NT ) {
         const int sy = i / LQ, c4 = i % LQ;
         const int gx0 = tx0 - 4 + 4 * c4;
-        const int gy  = min( max( ty0 - 1 + sy, 0 ), h - 1 );
+        const int gy  = min( max( ty0 - 1 + sy, dv.y_lo ), dv.y_hi - 1 );
         float4* d = reinterpret_cast<float4*>( D + sy * EX_SW ) + c4;
         const bool ok = ( gx0 >= 0 ) && ( gx0 + 3 < dv.pitch );
         const float4* p = reinterpret_cast<const float4*>( dv.base + (size_t)gy * dv.pitch + ( ok ? gx0 : 0 ) );
@@ -272,6 +274,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
         for( int j = 0; j < 4; j++ ) {
             const int gx = tx0 + 4 * g + j;
             bool in = ( gx >= 1 ) && ( gy >= 1 ) && ( gx <= w - 2 ) && ( gy <= h - 2 );
+            in = in && ( gy >= L.own_lo[o] ) && ( gy < L.own_hi[o] );       /* banded: each voxel belongs to one context */
             if( MODE == PSIFT_MODE_OPENCV ) in = in && !( gx < 5 || gy < 5 || gx >= w - 5 || gy >= h - 5 );   /* :336-340 */
             inside |= in ? ( 1u << j ) : 0u;
         }
@@ -394,11 +397,12 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     for( int o = 0; o < L.n_oct; o++ ) {
         G.first_block[o] = nb;
         const int tx = ( L.w[o] + EX_TX - 1 ) / EX_TX;
-        const int ty = ( L.h[o] + EX_TY - 1 ) / EX_TY;
+        const int ty = ( L.row_hi[o] - L.row_lo[o] + EX_TY - 1 ) / EX_TY;
         G.tiles_x[o] = tx;
-        nb += tx * ty;
+        if( o >= L.oct_begin && o < L.oct_end ) nb += tx * ty;          /* octaves outside the pass get no blocks */
     }
     for( int o = L.n_oct; o <= MAX_OCT; o++ ) G.first_block[o] = nb;
+    if( nb == 0 ) return cudaErrorInvalidValue;
     const size_t smem = extrema_smem( L.n_lvl );
     if( L.n_lvl > 60 ) return cudaErrorInvalidValue;                      /* queue entries hold 6 bits of level */
 #define PSIFT_EXT_LAUNCH( MODE )                                                                             \

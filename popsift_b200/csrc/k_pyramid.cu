@@ -38,7 +38,9 @@ struct BlurArgs {
     cudaTextureObject_t tex;      /* input image (FROM_TEX only) */
     float*              dst;
     float*              ds_dst;   /* level 0 of the next octave, or nullptr */
-    int   w, h, pitch;
+    int   w, h, pitch;            /* h: height of the whole plane (normalised texture coordinates) */
+    int   y_lo, y_hi;             /* rows [y_lo, y_hi) are stored and computed here (the whole plane unless banded);
+                                     src/dst/ds_dst point at the plane's row 0 even when that row is not stored */
     int   ds_pitch;
     float shift;                  /* FROM_TEX: texel shift, s_pyramid_build.cu:110-114 */
     Taps  th, tv;
@@ -57,7 +59,7 @@ k_blur_level( const __grid_constant__ BlurArgs a )
 
     const int tid = threadIdx.x;
     const int tx0 = blockIdx.x * TX;
-    const int ty0 = blockIdx.y * TY;
+    const int ty0 = a.y_lo + blockIdx.y * TY;
     const int w = a.w, h = a.h;
     /* all SH rows are staged and filtered, including the <= 3 padding rows whose taps are zero:
      * 0 * (uninitialised shared memory) could be NaN */
@@ -74,7 +76,7 @@ k_blur_level( const __grid_constant__ BlurArgs a )
              * a different texel than "last octave pixel" when the input is downscaled.  y is
              * clamped to the octave: the reference's vertical pass clamps on its row buffer. */
             const int gx = tx0 - HALO + c;
-            const int gy = min( max( ty0 - HALO + r, 0 ), h - 1 );
+            const int gy = min( max( ty0 - HALO + r, a.y_lo ), a.y_hi - 1 );
             const float rx = __fdiv_rn( (float)gx + a.shift, fw );
             const float ry = __fdiv_rn( (float)gy + a.shift, fh );
             S[r * SW + c] = tex2D<float>( a.tex, rx, ry );
@@ -85,7 +87,7 @@ k_blur_level( const __grid_constant__ BlurArgs a )
             constexpr int SW4 = SW / 4;
             for( int i = tid; i < ( r_hi - r_lo ) * SW4; i += NT ) {
                 const int r = r_lo + i / SW4, c4 = i % SW4;
-                const int gy = min( max( ty0 - HALO + r, 0 ), h - 1 );
+                const int gy = min( max( ty0 - HALO + r, a.y_lo ), a.y_hi - 1 );
                 const float4 v = __ldg( reinterpret_cast<const float4*>( a.src + (size_t)gy * a.pitch + ( tx0 - HALO ) ) + c4 );
                 reinterpret_cast<float4*>( S + r * SW )[c4] = v;
             }
@@ -93,7 +95,7 @@ k_blur_level( const __grid_constant__ BlurArgs a )
             for( int i = tid; i < ( r_hi - r_lo ) * SW; i += NT ) {
                 const int r = r_lo + i / SW, c = i % SW;
                 const int gx = min( max( tx0 - HALO + c, 0 ), w - 1 );
-                const int gy = min( max( ty0 - HALO + r, 0 ), h - 1 );
+                const int gy = min( max( ty0 - HALO + r, a.y_lo ), a.y_hi - 1 );
                 S[r * SW + c] = __ldg( a.src + (size_t)gy * a.pitch + gx );
             }
         }
@@ -152,7 +154,7 @@ k_blur_level( const __grid_constant__ BlurArgs a )
             }
             acc = __fmaf_rn( win[HALO + j], a.tv.g[0], acc );
             const int gy = ty0 + y0 + j;
-            if( gx < w && gy < h ) {
+            if( gx < w && gy < a.y_hi ) {
                 a.dst[(size_t)gy * a.pitch + gx] = acc;
                 if( a.ds_dst && !( ( gx | gy ) & 1 ) )
                     a.ds_dst[(size_t)( gy >> 1 ) * a.ds_pitch + ( gx >> 1 )] = acc;
@@ -231,9 +233,9 @@ k_blur2( const __grid_constant__ BlurArgs a )
     float*  I  = smem + 2 * RP * SW;                  /* [2*RP][TXv]  horizontal result, row-major */
 
     const int tid = threadIdx.x;
-    const int tx0 = blockIdx.x * TXv, ty0 = blockIdx.y * TYv;
+    const int tx0 = blockIdx.x * TXv, ty0 = a.y_lo + blockIdx.y * TYv;
     const int w = a.w, h = a.h;
-    const int nrow = min( TYv, h - ty0 );            /* output rows / columns this tile really has */
+    const int nrow = min( TYv, a.y_hi - ty0 );            /* output rows / columns this tile really has */
     const int ncol = min( TXv, w - tx0 );
     const int RPn  = ( nrow + 2 * H + 1 ) >> 1;
     const int ng   = ( ncol + 3 ) >> 2;              /* groups of 4 output columns */
@@ -252,8 +254,8 @@ k_blur2( const __grid_constant__ BlurArgs a )
         #pragma unroll
         for( int k = 0; k < NC; k++ ) rx[k] = __fdiv_rn( (float)( tx0 - HX + lane + 32 * k ) + a.shift, fw );   /* x unclamped: see k_blur_level */
         for( int p = wid; p < RPn; p += NT / 32 ) {
-            const int g0 = min( max( ty0 - H + 2 * p,     0 ), h - 1 );
-            const int g1 = min( max( ty0 - H + 2 * p + 1, 0 ), h - 1 );
+            const int g0 = min( max( ty0 - H + 2 * p, a.y_lo ), a.y_hi - 1 );
+            const int g1 = min( max( ty0 - H + 2 * p + 1, a.y_lo ), a.y_hi - 1 );
             const float ry0 = __fdiv_rn( (float)g0 + a.shift, fh ), ry1 = __fdiv_rn( (float)g1 + a.shift, fh );
             #pragma unroll
             for( int k = 0; k < NC; k++ ) {
@@ -271,8 +273,8 @@ k_blur2( const __grid_constant__ BlurArgs a )
             for( int u = 0; u < 4; u++ ) {
                 const int i = min( i0 + u * NT, RPn * SW - 1 );
                 const int p = i / SW, c = i % SW;
-                const int g0 = min( max( ty0 - H + 2 * p,     0 ), h - 1 );
-                const int g1 = min( max( ty0 - H + 2 * p + 1, 0 ), h - 1 );
+                const int g0 = min( max( ty0 - H + 2 * p, a.y_lo ), a.y_hi - 1 );
+                const int g1 = min( max( ty0 - H + 2 * p + 1, a.y_lo ), a.y_hi - 1 );
                 const int gx = min( max( tx0 - HX + c, 0 ), w - 1 );
                 v[u] = make_float2( __ldg( a.src + (size_t)g0 * a.pitch + gx ), __ldg( a.src + (size_t)g1 * a.pitch + gx ) );
             }
@@ -288,8 +290,8 @@ k_blur2( const __grid_constant__ BlurArgs a )
         #pragma unroll T::UNR
         for( int i = tid; i < RPn * SQ; i += NT ) {
             const int p = i / SQ, c4 = i % SQ;
-            const int g0 = min( max( ty0 - H + 2 * p,     0 ), h - 1 );
-            const int g1 = min( max( ty0 - H + 2 * p + 1, 0 ), h - 1 );
+            const int g0 = min( max( ty0 - H + 2 * p, a.y_lo ), a.y_hi - 1 );
+            const int g1 = min( max( ty0 - H + 2 * p + 1, a.y_lo ), a.y_hi - 1 );
             const float4 A = __ldg( reinterpret_cast<const float4*>( a.src + (size_t)g0 * a.pitch + ( tx0 - HX ) ) + c4 );
             const float4 B = __ldg( reinterpret_cast<const float4*>( a.src + (size_t)g1 * a.pitch + ( tx0 - HX ) ) + c4 );
             S4[p * 2 * SQ + c4]      = make_float4( A.x, B.x, A.y, B.y );
@@ -343,7 +345,7 @@ k_blur2( const __grid_constant__ BlurArgs a )
         float2 win[VYv + 2 * H];
         #pragma unroll
         for( int k = 0; k < VYv + 2 * H; k++ ) win[k] = *reinterpret_cast<const float2*>( I + ( y0 + k ) * TXv + 2 * cp );
-        const int   nval = min( VYv, h - ( ty0 + y0 ) );
+        const int   nval = min( VYv, a.y_hi - ( ty0 + y0 ) );
         const bool  pair = gx + 1 < w;
         float*      row0 = a.dst + (size_t)( ty0 + y0 ) * a.pitch + gx;
         float*      ds0  = a.ds_dst ? a.ds_dst + (size_t)( ( ty0 + y0 ) >> 1 ) * a.ds_pitch + ( gx >> 1 ) : nullptr;
@@ -386,7 +388,7 @@ static cudaError_t launch_v2t( const BlurArgs& a, cudaStream_t st )
         if( e != cudaSuccess ) return e;
         if( dev < 16 ) attr_done[dev] = true;
     }
-    dim3 grid( ( a.w + T::TXv - 1 ) / T::TXv, ( a.h + T::TYv - 1 ) / T::TYv );
+    dim3 grid( ( a.w + T::TXv - 1 ) / T::TXv, ( a.y_hi - a.y_lo + T::TYv - 1 ) / T::TYv );
     k_blur2<H, FROM_TEX, T><<<grid, NT, smem, st>>>( a );
     return cudaGetLastError();
 }
@@ -394,7 +396,7 @@ static cudaError_t launch_v2t( const BlurArgs& a, cudaStream_t st )
 template<int H, bool FROM_TEX>
 static cudaError_t launch_v2( const BlurArgs& a, cudaStream_t st )
 {
-    if( (long)a.w * a.h <= blur_small_max() ) return launch_v2t<H, FROM_TEX, TileSm>( a, st );
+    if( (long)a.w * ( a.y_hi - a.y_lo ) <= blur_small_max() ) return launch_v2t<H, FROM_TEX, TileSm>( a, st );
     return launch_v2t<H, FROM_TEX, TileMed>( a, st );
 }
 
@@ -440,7 +442,7 @@ static cudaError_t launch_hq( const BlurArgs& a, cudaStream_t st )
     } else if( dev >= 8 ) {
         cudaFuncSetAttribute( k_blur_level<HQ, FROM_TEX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem );
     }
-    dim3 grid( ( a.w + TX - 1 ) / TX, ( a.h + TY - 1 ) / TY );
+    dim3 grid( ( a.w + TX - 1 ) / TX, ( a.y_hi - a.y_lo + TY - 1 ) / TY );
     k_blur_level<HQ, FROM_TEX><<<grid, NT, smem, st>>>( a );
     return cudaGetLastError();
 }
@@ -478,7 +480,9 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
     const bool fork = S.side[0] != nullptr;
     bool side_used[2] = { false, false };
     cudaError_t e;
-    for( int o = 0; o < L.n_oct; o++ ) {
+    for( int o = L.oct_begin; o < L.oct_end; o++ ) {
+        /* level 0 of octave 0 comes from the input image, of any other octave from the previous
+         * octave's fused downscale (or, for the first octave of a seeded pass, from the caller) */
         for( int l = ( o == 0 ? 0 : 1 ); l < L.n_lvl; l++ ) {
             cudaStream_t st = S.chain;
             if( fork && l > ds_level ) {
@@ -491,9 +495,10 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
             }
             BlurArgs a;
             a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
+            a.y_lo = L.row_lo[o]; a.y_hi = L.row_hi[o];
             a.dst = L.base[o] + (size_t)l * L.lstride[o];
             a.ds_dst = nullptr; a.ds_pitch = 0;
-            if( l == ds_level && o + 1 < L.n_oct ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
+            if( l == ds_level && o + 1 < L.alloc_end ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
             a.shift = shift;
             if( o == 0 && direct_o0 ) {
                 a.src = nullptr; a.tex = input_tex;

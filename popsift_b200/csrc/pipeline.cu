@@ -53,6 +53,7 @@ struct Slot {
     float* arena = nullptr; size_t arena_floats = 0;
     PyrLayout L;
     int in_w = 0, in_h = 0;
+    int reg_kind = 0, reg_a = 0, reg_b = 0, reg_c = 0;     /* region the layout was built for (see Region) */
     std::vector<cudaTextureObject_t> lintex_h;
     cudaTextureObject_t* lintex_d = nullptr;
 
@@ -134,9 +135,32 @@ static void free_slot( Slot& s )
 
 /* (re)build the pyramid geometry of a slot for an input size (Pyramid::Pyramid / resetDimensions,
  * sift_pyramid.cu:108-177; octave sizes by repeated ceil(/2), :132-134) */
-static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h )
+/* What a job covers: the whole image (the normal case), a row band of a giant image up to a
+ * split octave, or the octaves above the split from a given level-0 plane. */
+struct Region {
+    int kind = 0;            /* 0 whole image, 1 band, 2 seeded upper octaves */
+    int y0 = 0, y1 = 0;      /* owned rows of octave 0 */
+    int split = 0;           /* band: last octave built; seeded: first octave built */
+};
+
+/* rows of octave 0 a band must hold so that everything it owns, in every octave up to `split`, is
+ * computed from exact data: the recurrence of SURVEY appendix A with this configuration's spans */
+static int band_halo_rows( const psift_ctx* c, int split )
 {
-    if( s.in_w == w && s.in_h == h && s.arena ) return PSIFT_OK;
+    const int n_lvl = c->cfg.levels + 3, ds_level = n_lvl - 3;
+    int s_all = 0, s_ds = 0;
+    for( int l = 1; l < n_lvl; l++ ) { s_all += c->gt.inc[l].span; if( l <= ds_level ) s_ds += c->gt.inc[l].span; }
+    const int s_0 = c->gt.dd[0].span + c->gt.inc[0].span;
+    /* window of the orientation / descriptor / refinement stages around a keypoint, octave pixels */
+    const int win = (int)ceilf( 3.6f * 3.0f * c->cfg.sigma * powf( 2.0f, (float)n_lvl / (float)c->cfg.levels ) ) + 16;
+    int e = win + s_all;
+    for( int o = split; o > 0; o-- ) e = std::max( 2 * e + s_ds + 2, win + s_all );
+    return e + s_0 + 2;
+}
+
+static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h, const Region& reg )
+{
+    if( s.in_w == w && s.in_h == h && s.arena && s.reg_kind == reg.kind && s.reg_a == reg.y0 && s.reg_b == reg.y1 && s.reg_c == reg.split ) return PSIFT_OK;
     int w0, h0;
     octave0_size( c->cfg, w, h, w0, h0 );
     const int n_oct = octave_count( c->cfg, w, h );
@@ -144,16 +168,41 @@ static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h )
     PyrLayout L;
     memset( &L, 0, sizeof L );
     L.n_oct = n_oct; L.n_lvl = n_lvl;
+    L.oct_begin = 0; L.oct_end = n_oct; L.alloc_end = n_oct;
+    if( reg.kind == 1 ) {
+        if( reg.split < 0 || reg.split >= n_oct ) return fail( PSIFT_E_INVALID, "split octave %d out of range (the image has %d octaves)", reg.split, n_oct );
+        L.oct_end = reg.split + 1; L.alloc_end = std::min( n_oct, reg.split + 2 );
+    } else if( reg.kind == 2 ) {
+        if( reg.split < 1 || reg.split >= n_oct ) return fail( PSIFT_E_INVALID, "first octave %d out of range (the image has %d octaves)", reg.split, n_oct );
+        L.oct_begin = reg.split;
+    }
+    if( reg.kind != 0 && ( reg.y0 < 0 || reg.y1 <= reg.y0 ) ) return fail( PSIFT_E_INVALID, "bad band rows [%d, %d)", reg.y0, reg.y1 );
     size_t total = 0;
     int ow = w0, oh = h0;
-    std::vector<size_t> off( n_oct );
+    std::vector<size_t> off( n_oct, 0 );
+    int lo0 = 0, hi0 = h0;
+    if( reg.kind == 1 ) {
+        const int halo = band_halo_rows( c, reg.split ), al = 1 << ( reg.split + 1 );
+        lo0 = std::max( 0, reg.y0 - halo ) / al * al;
+        hi0 = std::min( h0, ( std::min( h0, reg.y1 ) + halo + al - 1 ) / al * al );
+    }
     for( int o = 0; o < n_oct; o++ ) {
         if( ow < 1 || oh < 1 ) return fail( PSIFT_E_INVALID, "image %dx%d too small for %d octaves", w, h, n_oct );
         L.w[o] = ow; L.h[o] = oh;
+        L.row_lo[o] = 0; L.row_hi[o] = oh; L.own_lo[o] = 0; L.own_hi[o] = oh;
+        if( reg.kind == 1 ) {
+            L.row_lo[o] = lo0 >> o;
+            L.row_hi[o] = std::min( oh, o == 0 ? hi0 : ( L.row_hi[o - 1] + 1 ) >> 1 );
+        }
+        if( reg.kind != 0 ) {
+            L.own_lo[o] = std::min( oh, reg.y0 >> o );
+            L.own_hi[o] = reg.y1 >= h0 ? oh : std::min( oh, reg.y1 >> o );
+        }
         L.pitch[o] = ( ow + 31 ) / 32 * 32;
-        L.lstride[o] = ( (size_t)L.pitch[o] * oh + 127 ) / 128 * 128;      /* keep planes 512-byte aligned (textures) */
+        const bool held = o >= L.oct_begin && o < L.alloc_end;
+        L.lstride[o] = held ? ( (size_t)L.pitch[o] * ( L.row_hi[o] - L.row_lo[o] ) + 127 ) / 128 * 128 : 0;   /* keep planes 512-byte aligned (textures) */
         off[o] = total;
-        total += L.lstride[o] * n_lvl;
+        total += L.lstride[o] * ( o < L.oct_end ? n_lvl : 1 );          /* the seed octave of a band holds level 0 only */
         ow = (int)ceilf( ow / 2.0f );
         oh = (int)ceilf( oh / 2.0f );
     }
@@ -165,13 +214,17 @@ static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h )
         for( auto t : s.lintex_h ) if( t ) cudaDestroyTextureObject( t );
         s.lintex_h.clear();
     }
-    for( int o = 0; o < n_oct; o++ ) L.base[o] = s.arena + off[o];
+    /* base[o] is where row 0 of the plane WOULD be: kernels address with global rows */
+    for( int o = 0; o < n_oct; o++ )
+        L.base[o] = reinterpret_cast<float*>( reinterpret_cast<uintptr_t>( s.arena + off[o] ) - sizeof(float) * (size_t)L.row_lo[o] * L.pitch[o] );
     s.L = L; s.in_w = w; s.in_h = h;
+    s.reg_kind = reg.kind; s.reg_a = reg.y0; s.reg_b = reg.y1; s.reg_c = reg.split;
 
     if( linear_needed( c->cfg.desc_mode ) ) {
         /* bilinear point-of-view of every Gaussian level (Octave::alloc_data_tex, sift_octave.cu:211-248) */
+        if( reg.kind == 1 ) return fail( PSIFT_E_INVALID, "banded extraction supports the loop and grid descriptor modes only" );
         s.lintex_h.assign( (size_t)n_oct * n_lvl, 0 );
-        for( int o = 0; o < n_oct; o++ )
+        for( int o = L.oct_begin; o < L.oct_end; o++ )
             for( int l = 0; l < n_lvl; l++ ) {
                 cudaResourceDesc rd; memset( &rd, 0, sizeof rd );
                 rd.resType = cudaResourceTypePitch2D;
@@ -446,13 +499,17 @@ void psift_destroy( psift_ctx* c )
     delete c;
 }
 
-static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pitch, int elem, bool on_device, psift_job** out )
+static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pitch, int elem, bool on_device, psift_job** out,
+                          const Region& reg = Region() )
 {
     if( !c || !out || !src ) return fail( PSIFT_E_INVALID, "null argument" );
+    if( reg.kind != 0 && c->cfg.filter_max_extrema > 0 ) return fail( PSIFT_E_INVALID, "the grid filter needs all keypoints of the image: not available for banded extraction" );
     *out = nullptr;
     if( w < 1 || h < 1 ) return fail( PSIFT_E_INVALID, "bad image size %dx%d", w, h );
-    if( pitch == 0 ) pitch = (size_t)w * elem;
-    if( pitch < (size_t)w * elem ) return fail( PSIFT_E_INVALID, "pitch smaller than a row" );
+    if( reg.kind != 2 ) {                 /* (a seeded pass checks its plane's pitch once the octave sizes are known) */
+        if( pitch == 0 ) pitch = (size_t)w * elem;
+        if( pitch < (size_t)w * elem ) return fail( PSIFT_E_INVALID, "pitch smaller than a row" );
+    }
     std::lock_guard<std::mutex> lk( c->mu );
     CU( cudaSetDevice( c->device ) );
     int si = -1;
@@ -463,10 +520,16 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
     if( si < 0 ) return fail( PSIFT_E_STATE, "all %d frame slots are in flight: wait for and free a job first", (int)c->slots.size() );
     c->next_slot = ( si + 1 ) % (int)c->slots.size();
     Slot& s = c->slots[si];
-    int rc = setup_pyramid( c, s, w, h );
+    int rc = setup_pyramid( c, s, w, h, reg );
     if( rc ) return rc;
     CU( cudaEventRecord( s.ev[0], s.stream ) );
-    if( on_device ) {
+    if( reg.kind == 2 ) {
+        /* src: level 0 of octave reg.split, whole plane, device memory, `pitch` bytes per row */
+        const PyrLayout& L = s.L;
+        const int o = reg.split;
+        if( pitch < (size_t)L.w[o] * 4 ) return fail( PSIFT_E_INVALID, "seed plane pitch smaller than a row of octave %d (%d pixels)", o, L.w[o] );
+        CU( cudaMemcpy2DAsync( L.base[o], (size_t)L.pitch[o] * 4, src, pitch, (size_t)L.w[o] * 4, L.h[o], cudaMemcpyDeviceToDevice, s.stream ) );
+    } else if( on_device ) {
         if( pitch % 32 || ( (uintptr_t)src % 512 ) )
             return fail( PSIFT_E_INVALID, "device image needs a 512-byte aligned base and a pitch that is a multiple of 32" );
         rc = bind_input_texture( s, src, pitch, w, h, elem );
@@ -505,6 +568,80 @@ int psift_submit_f32( psift_ctx* c, int w, int h, const float* host, size_t pitc
 { return submit_common( c, w, h, host, pitch, 4, false, out ); }
 int psift_submit_dev_u8( psift_ctx* c, int w, int h, const uint8_t* dev, size_t pitch, psift_job** out )
 { return submit_common( c, w, h, dev, pitch, 1, true, out ); }
+
+int psift_band_plan( const psift_config* cfg, int w, int h, int parts, int max_seed_pixels, int* split_octave, int* bounds )
+{
+    if( !cfg || parts < 1 || !split_octave || !bounds ) return fail( PSIFT_E_INVALID, "null argument" );
+    int w0, h0;
+    octave0_size( *cfg, w, h, w0, h0 );
+    const int n_oct = octave_count( *cfg, w, h );
+    if( n_oct < 2 ) return fail( PSIFT_E_INVALID, "an image with one octave cannot be split" );
+    if( max_seed_pixels <= 0 ) max_seed_pixels = 2048 * 2048;
+    /* the octaves above the split are finished un-split: pick the first split whose seed is small */
+    int k = 0, ow = w0, oh = h0;
+    for( ;; ) {
+        const int nw = ( ow + 1 ) / 2, nh = ( oh + 1 ) / 2;
+        if( (long long)nw * nh <= max_seed_pixels || k + 2 >= n_oct ) break;
+        ow = nw; oh = nh; k++;
+    }
+    *split_octave = k;
+    const int al = 1 << ( k + 1 );
+    for( int p = 0; p <= parts; p++ ) {
+        long long y = (long long)h0 * p / parts;
+        y = ( y + al / 2 ) / al * al;
+        bounds[p] = (int)std::min<long long>( y, h0 );
+    }
+    bounds[0] = 0; bounds[parts] = h0;
+    for( int p = 0; p < parts; p++ ) if( bounds[p + 1] <= bounds[p] ) return fail( PSIFT_E_INVALID, "image too small for %d bands", parts );
+    return PSIFT_OK;
+}
+
+int psift_submit_band_u8( psift_ctx* c, int w, int h, const uint8_t* img, size_t pitch, int on_device,
+                          int y0, int y1, int split_octave, psift_job** out )
+{
+    Region r; r.kind = 1; r.y0 = y0; r.y1 = y1; r.split = split_octave;
+    if( split_octave >= 0 && ( ( y0 & ( ( 1 << ( split_octave + 1 ) ) - 1 ) ) != 0 ) )
+        return fail( PSIFT_E_INVALID, "band start %d must be a multiple of 2^(split+1)", y0 );
+    return submit_common( c, w, h, img, pitch, 1, on_device != 0, out, r );
+}
+
+int psift_band_seed( psift_job* j, const float** dev_rows, int* pitch_floats, int* row_lo, int* row_hi, int* seed_w, int* seed_h )
+{
+    if( !j || !dev_rows ) return fail( PSIFT_E_INVALID, "null argument" );
+    const Slot& s = j->ctx->slots[j->slot];
+    const PyrLayout& L = s.L;
+    if( s.reg_kind != 1 || L.oct_end >= L.alloc_end ) return fail( PSIFT_E_STATE, "not a band job, or no octave above the split" );
+    const int o = L.oct_end;
+    *dev_rows = L.base[o] + (size_t)L.row_lo[o] * L.pitch[o];
+    if( pitch_floats ) *pitch_floats = L.pitch[o];
+    if( row_lo ) *row_lo = L.row_lo[o];
+    if( row_hi ) *row_hi = L.row_hi[o];
+    if( seed_w ) *seed_w = L.w[o];
+    if( seed_h ) *seed_h = L.h[o];
+    return PSIFT_OK;
+}
+
+int psift_band_seed_copy( psift_job* j, float* dst_dev, size_t dst_pitch_bytes, int row_from, int row_to )
+{
+    if( !j || !dst_dev ) return fail( PSIFT_E_INVALID, "null argument" );
+    const Slot& s = j->ctx->slots[j->slot];
+    const PyrLayout& L = s.L;
+    if( s.reg_kind != 1 || L.oct_end >= L.alloc_end ) return fail( PSIFT_E_STATE, "not a band job, or no octave above the split" );
+    const int o = L.oct_end;
+    if( row_from < L.row_lo[o] || row_to > L.row_hi[o] || row_to <= row_from ) return fail( PSIFT_E_INVALID, "rows [%d,%d) outside the band's seed rows [%d,%d)", row_from, row_to, L.row_lo[o], L.row_hi[o] );
+    CU( cudaSetDevice( j->ctx->device ) );
+    CU( cudaMemcpy2DAsync( dst_dev, dst_pitch_bytes, L.base[o] + (size_t)row_from * L.pitch[o], (size_t)L.pitch[o] * 4,
+                           (size_t)L.w[o] * 4, row_to - row_from, cudaMemcpyDeviceToDevice, s.stream ) );
+    CU( cudaStreamSynchronize( s.stream ) );
+    return PSIFT_OK;
+}
+
+int psift_submit_seed_dev_f32( psift_ctx* c, int w, int h, int first_octave, const float* dev_plane, size_t pitch_bytes,
+                               int y0, int y1, psift_job** out )
+{
+    Region r; r.kind = 2; r.y0 = y0; r.y1 = y1; r.split = first_octave;
+    return submit_common( c, w, h, dev_plane, pitch_bytes, 4, true, out, r );
+}
 
 int psift_wait( psift_job* j, psift_result* r )
 {

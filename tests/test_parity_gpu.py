@@ -210,3 +210,37 @@ def test_cuda_path_against_cpu_oracle(tmp_path, w, h, seed, flags):
     assert rep["max_dsigma_rel"] < 1e-6 and rep["max_dtheta"] < parity.TOL_THETA, rep
     # grid rounds sample positions; iloop samples through the bilinear unit, blended in float on the CPU
     assert rep["max_desc_l2"] < (0.05 if "grid" in flags else 2e-2 if "iloop" in flags else parity.TOL_DESC), rep
+
+
+def _canon(r):
+    """order-independent view of an extraction: per keypoint (octave, x, y, sigma, num_ori, orientations) and
+    its descriptors, sorted"""
+    order = np.lexsort((r.ext["x"], r.ext["y"], r.ext["lpos"], r.ext["octave"]))
+    e = r.ext[order]
+    d = [r.desc[e["idx_ori"][i]: e["idx_ori"][i] + e["num_ori"][i]].tobytes() for i in range(len(e))]
+    keys = [(int(x["octave"]), int(x["lpos"]), x["x"].tobytes(), x["y"].tobytes(), x["sigma"].tobytes(), int(x["num_ori"]), x["ori"].tobytes()) for x in e]
+    return keys, d
+
+
+@pytest.mark.parametrize("w,h,parts,seed_px,flags", [
+    (1024, 1536, 2, 128 * 192, []),                       # split at octave 2, two bands
+    (1024, 1536, 3, 512 * 768, ["--downsampling", "0"]),  # split at octave 0, three bands
+    (800, 2048, 4, 100 * 256, ["--desc-mode", "grid", "--mode", "vlfeat"]),
+    (640, 1000, 2, 1, []),                                # every octave but the last two banded
+])
+def test_banded_equals_whole(w, h, parts, seed_px, flags):
+    """one image cut in row bands (+ one gather of the seed plane) gives the un-split result bit for
+    bit -- keypoints, orientations and descriptors.  Bands run one after the other on one GPU here; the
+    multi-GPU driver (popsift_b200/banded.py: extract_banded_dist) runs the same C-ABI calls per rank."""
+    from popsift_b200 import banded
+    img = synth.gen(w, h, 77 + parts)
+    cfg = capi.config_from_flags(flags)
+    with capi.Context(cfg) as ctx:
+        whole = ctx.extract(img)
+        tiled, split, bounds = banded.extract_banded_local(ctx, img, parts, cfg, seed_px)
+    assert len(bounds) == parts + 1 and bounds[0] == 0
+    assert tiled.n_feat == whole.n_feat and tiled.n_desc == whole.n_desc, (tiled.n_feat, whole.n_feat, split, bounds)
+    assert np.array_equal(np.asarray(tiled.ext_ct), np.asarray(whole.ext_ct))
+    ka, da = _canon(tiled); kb, db = _canon(whole)
+    assert ka == kb
+    assert da == db
