@@ -131,3 +131,22 @@ def test_two_rank_gloo_timing_and_sharding(tmp_path):
                        capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert r.stdout.count("ok") == 2
+
+
+def test_band_plan_partitions_rows():
+    """psift_band_plan (host logic of the banded mode): bands partition the rows of octave 0, start on
+    multiples of 2^(split+1), and the seed rows the bands contribute partition the seed plane."""
+    from popsift_b200 import banded
+    cfg = capi.default_config(downsampling=0)
+    for (w, h, parts) in [(16384, 16384, 8), (8192, 8192, 2), (4000, 3001, 3), (1024, 1536, 4)]:
+        split, b = capi.band_plan(cfg, w, h, parts)
+        w0, h0, n_oct = capi.geometry(cfg, w, h)
+        assert b[0] == 0 and b[-1] == h0 and all(b[i] < b[i + 1] for i in range(parts))
+        assert all(v % (1 << (split + 1)) == 0 for v in b[:-1])
+        assert 0 <= split < n_oct - 1
+        sh = h0
+        for _ in range(split + 1): sh = (sh + 1) // 2
+        rows = [banded._own_seed_rows(b, r, split, sh) for r in range(parts)]
+        assert rows[0][0] == 0 and rows[-1][1] == sh and all(rows[i][1] == rows[i + 1][0] for i in range(parts - 1))
+    split, _ = capi.band_plan(cfg, 16384, 16384, 8)
+    assert split == 2                                   # octave 3 of a 16384^2 image is 2048^2: finished un-split
