@@ -150,3 +150,17 @@ def test_band_plan_partitions_rows():
         assert rows[0][0] == 0 and rows[-1][1] == sh and all(rows[i][1] == rows[i + 1][0] for i in range(parts - 1))
     split, _ = capi.band_plan(cfg, 16384, 16384, 8)
     assert split == 2                                   # octave 3 of a 16384^2 image is 2048^2: finished un-split
+
+
+def test_demo_cli_fails_loudly_without_gpu(tmp_path):
+    """popsift-demo (apps/popsift_demo.cpp) parses the reference's flags; with no CUDA device it must say so and
+    fail, not fall back to anything."""
+    import subprocess
+    exe = os.path.join(ROOT, "popsift_b200", "popsift-demo")
+    if not os.path.exists(exe): pytest.skip("popsift-demo not built")
+    r = subprocess.run([exe, "--no-such-flag"], capture_output=True, text=True)
+    assert r.returncode != 0 and "unrecognised option" in r.stderr
+    if capi.lib().psift_device_count() > 0: return
+    p = tmp_path / "a.pgm"; p.write_bytes(b"P5\n4 4\n255\n" + bytes(16))
+    r = subprocess.run([exe, "-i", str(p), "--desc-mode", "grid"], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode != 0 and "no CUDA device" in r.stderr

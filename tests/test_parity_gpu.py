@@ -244,3 +244,24 @@ def test_banded_equals_whole(w, h, parts, seed_px, flags):
     ka, da = _canon(tiled); kb, db = _canon(whole)
     assert ka == kb
     assert da == db
+
+
+def test_popsift_demo_cli(tmp_path):
+    """The reference's command line (src/application/main.cpp) on a P5 and a P6 file: output-features.txt holds one
+    line per descriptor, `x y 1/s^2 0 1/s^2 d0..d127` (features.cu:308-328), and matches the golden run."""
+    exe = os.path.join(ROOT, "popsift_b200", "popsift-demo")
+    if not os.path.exists(exe): pytest.skip("popsift-demo not built")
+    img = load("g256"); h, w = img.shape
+    ref = refio.RefFeatures(os.path.join(refio.GOLD, "ref", "g256_default.feat.bin"))
+    pgm = tmp_path / "a.pgm"; pgm.write_bytes(b"P5\n# comment\n%d %d\n255\n" % (w, h) + img.tobytes())
+    ppm = tmp_path / "b.ppm"; ppm.write_bytes(b"P6 %d %d 255\n" % (w, h) + np.repeat(img[:, :, None], 3, 2).tobytes())
+    for f in (pgm, ppm):
+        r = subprocess.run([exe, "-i", str(f), "--norm-multi=9", "--write-as-uchar"], cwd=tmp_path, capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stderr[-500:]
+        assert "Number of feature points: %d number of feature descriptors: %d" % (ref.n_feat, ref.n_desc) in r.stderr
+        rows = [l.split() for l in (tmp_path / "output-features.txt").read_text().splitlines()]
+        assert len(rows) == ref.n_desc and all(len(x) == 5 + 128 for x in rows)
+        xs = sorted(round(float(x[0]), 2) for x in rows)
+        want = sorted(round(float(f["x"]), 2) for f in ref.feat for _ in range(int(f["num_ori"])))
+        assert np.allclose(xs, want, atol=0.011)
+        assert all(float(v) == int(float(v)) and 0 <= float(v) <= 512 for x in rows[:5] for v in x[5:])
