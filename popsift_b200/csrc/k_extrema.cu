@@ -213,6 +213,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
 {
     extern __shared__ __align__( 16 ) float ex_smem[];
     __shared__ int n1, n2;
+    pdl_enter();
     const int n_lvl = NLVL ? NLVL : L.n_lvl;
     const int qcap  = ( n_lvl - 3 ) * EX_TX * EX_TY;
     float*          D  = ex_smem;                                             /* [n_lvl-1][EX_SH][EX_SW] */
@@ -347,6 +348,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
  * and flag overflow.  One thread. */
 __global__ void k_extrema_finish( Counters* ct, int n_oct, int max_extrema, int ext_capacity )
 {
+    pdl_enter();
     if( threadIdx.x != 0 || blockIdx.x != 0 ) return;
     int ps = 0;
     for( int o = 0; o < MAX_OCT; o++ ) {
@@ -369,6 +371,7 @@ __global__ void __launch_bounds__( RS_NT )
 k_rank_sort( const Cand* cand, int cand_stride, const Counters* ct, int n_oct, Cand* sorted )
 {
     __shared__ unsigned long long keys[RS_NT];
+    pdl_enter();
     const int o = blockIdx.y;
     const int n = ct->ext_ct[o];
     const Cand* src = cand + (size_t)o * cand_stride;
@@ -407,11 +410,11 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     if( L.n_lvl > 60 ) return cudaErrorInvalidValue;                      /* queue entries hold 6 bits of level */
 #define PSIFT_EXT_LAUNCH( MODE )                                                                             \
     do {                                                                                                      \
-        if( L.n_lvl == 6 ) k_extrema<MODE, 6><<<nb, EX_NT, smem, st>>>( L, G, K, cand, cand_stride, ct );      \
+        if( L.n_lvl == 6 ) launch_pdl( k_extrema<MODE, 6>, dim3( nb ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct ); \
         else {                                                                                                \
             cudaError_t e = cudaFuncSetAttribute( k_extrema<MODE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem ); \
             if( e != cudaSuccess ) return e;                                                                  \
-            k_extrema<MODE, 0><<<nb, EX_NT, smem, st>>>( L, G, K, cand, cand_stride, ct );                     \
+            launch_pdl( k_extrema<MODE, 0>, dim3( nb ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct );       \
         }                                                                                                     \
     } while( 0 )
     switch( K.sift_mode ) {
@@ -420,8 +423,8 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     default:                PSIFT_EXT_LAUNCH( PSIFT_MODE_POPSIFT ); break;
     }
 #undef PSIFT_EXT_LAUNCH
-    k_extrema_finish<<<1, 32, 0, st>>>( ct, L.n_oct, K.max_extrema, ext_capacity );
-    k_rank_sort<<<dim3( 8, L.n_oct ), RS_NT, 0, st>>>( cand, cand_stride, ct, L.n_oct, sorted );
+    launch_pdl( k_extrema_finish, dim3( 1 ), dim3( 32 ), 0, st, ct, L.n_oct, K.max_extrema, ext_capacity );
+    launch_pdl( k_rank_sort, dim3( 8, L.n_oct ), dim3( RS_NT ), 0, st, cand, cand_stride, ct, L.n_oct, sorted );
     if( launches ) *launches += 3;
     return cudaGetLastError();
 }

@@ -31,6 +31,7 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
     __shared__ float yv[ORI_WARPS][64];
     __shared__ float ang[ORI_WARPS][64];
 
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int wid  = threadIdx.x >> 5;
     const int total = ct->ext_total;
@@ -175,6 +176,7 @@ k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* 
 {
     __shared__ int warp_sum[32];
     __shared__ int carry;
+    pdl_enter();
     const int total = ct->ext_total;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if( threadIdx.x == 0 ) carry = 0;
@@ -235,8 +237,8 @@ k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* 
 cudaError_t launch_orientation( const PyrLayout& L, const Cand* sorted, Counters* ct, psift_extremum* ext,
                                 int* desc_map, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches )
 {
-    k_orientation<<<n_blocks, ORI_WARPS * 32, 0, st>>>( L, sorted, ct, ext );
-    k_ori_prefix<<<1, PS_NT, 0, st>>>( ext, ct, desc_map, desc_capacity );
+    launch_pdl( k_orientation, dim3( n_blocks ), dim3( ORI_WARPS * 32 ), 0, st, L, sorted, ct, ext );
+    launch_pdl( k_ori_prefix, dim3( 1 ), dim3( PS_NT ), 0, st, ext, ct, desc_map, desc_capacity );
     if( launches ) *launches += 2;
     return cudaGetLastError();
 }

@@ -25,8 +25,16 @@
 #include "common.h"
 #include "kernels.h"
 #include <cstdlib>
+#include <algorithm>
 
 namespace psift {
+
+bool pdl_enabled()
+{
+    static int v = -1;
+    if( v < 0 ) v = getenv( "PSIFT_NO_PDL" ) ? 0 : 1;
+    return v != 0;
+}
 
 constexpr int TX = 128;      /* tile width  (outputs) */
 constexpr int TY = 32;       /* tile height (outputs) */
@@ -235,6 +243,9 @@ k_blur2( const __grid_constant__ BlurArgs a )
     const int tid = threadIdx.x;
     const int tx0 = blockIdx.x * TXv, ty0 = a.y_lo + blockIdx.y * TYv;
     const int w = a.w, h = a.h;
+    /* programmatic dependent launch: let the next level's blocks be scheduled while this grid runs,
+     * and do not touch the previous level's output before that grid has completed and flushed */
+    pdl_enter();
     const int nrow = min( TYv, a.y_hi - ty0 );            /* output rows / columns this tile really has */
     const int ncol = min( TXv, w - tx0 );
     const int RPn  = ( nrow + 2 * H + 1 ) >> 1;
@@ -389,8 +400,7 @@ static cudaError_t launch_v2t( const BlurArgs& a, cudaStream_t st )
         if( dev < 16 ) attr_done[dev] = true;
     }
     dim3 grid( ( a.w + T::TXv - 1 ) / T::TXv, ( a.y_hi - a.y_lo + T::TYv - 1 ) / T::TYv );
-    k_blur2<H, FROM_TEX, T><<<grid, NT, smem, st>>>( a );
-    return cudaGetLastError();
+    return launch_pdl( k_blur2<H, FROM_TEX, T>, grid, dim3( NT ), smem, st, a );
 }
 
 template<int H, bool FROM_TEX>
