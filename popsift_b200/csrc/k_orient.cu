@@ -19,7 +19,7 @@ namespace psift {
 __device__ static const float PI_F  = 3.14159265358979323846f;          /* sift_constants.h:27-36 */
 __device__ static const float PI2_F = 2.0f * 3.14159265358979323846f;
 
-constexpr int ORI_WARPS = 8;
+constexpr int ORI_WARPS = 4;
 
 __global__ void __launch_bounds__( ORI_WARPS * 32 )
 k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ cand, Counters* __restrict__ ct,
@@ -31,16 +31,22 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
     __shared__ float yv[ORI_WARPS][64];
     __shared__ float ang[ORI_WARPS][64];
 
+    __shared__ float part[ORI_WARPS][ORI_NBINS];
+    __shared__ int   next_e;
+
     pdl_enter();
-    const int lane = threadIdx.x & 31;
-    const int wid  = threadIdx.x >> 5;
+    const int tid  = threadIdx.x;
+    const int lane = tid & 31;
+    const int wid  = tid >> 5;
     const int total = ct->ext_total;
 
-    /* keypoints are handed out one at a time per warp: their windows differ in size by 5x and more */
+    /* a block per keypoint, handed out one at a time (windows differ in size by 5x and more): all
+     * eight warps share the window, each lane summing into its own histogram column, and the
+     * columns are added up in a fixed order - reproducible, unlike the reference's atomics */
     for( ;; ) {
-        int e = 0;
-        if( lane == 0 ) e = atomicAdd( &ct->ori_next, 1 );
-        e = __shfl_sync( 0xffffffffu, e, 0 );
+        if( tid == 0 ) next_e = atomicAdd( &ct->ori_next, 1 );
+        __syncthreads();
+        const int e = next_e;
         if( e >= total ) break;
         int o = 0;
         while( o + 1 < L.n_oct && e >= ct->ext_ps[o + 1] ) o++;
@@ -66,10 +72,11 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
         const int pitch = L.pitch[o];
         const float* plane = L.base[o] + (size_t)min( max( level, 0 ), L.n_lvl - 1 ) * L.lstride[o];
         const int wxs = max( wx, 1 );
-        const int q = 32 / wxs, r = 32 - q * wxs;                           /* (row, column) advance per 32 pixels */
-        int yy = ymin + lane / wxs, xx = xmin + lane % wxs;
+        constexpr int NTH = ORI_WARPS * 32;
+        const int q = NTH / wxs, r = NTH - q * wxs;                         /* (row, column) advance per NTH pixels */
+        int yy = ymin + tid / wxs, xx = xmin + tid % wxs;
 
-        for( int i = lane; i < loops; i += 32 ) {
+        for( int i = tid; i < loops; i += NTH ) {
             /* 1 <= xx <= w-2 and 1 <= yy <= h-2: the four neighbours are inside the plane */
             const float* p = plane + (size_t)yy * pitch + xx;
             const float gx = __fsub_rn( __ldg( p + 1 ), __ldg( p - 1 ) );
@@ -87,11 +94,20 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
             }
             yy += q; xx += r; if( xx > xmax ) { xx -= wx; yy++; }
         }
-        __syncwarp();
-        for( int b = lane; b < ORI_NBINS; b += 32 ) {
+        __syncthreads();
+        for( int i = tid; i < ORI_WARPS * ORI_NBINS; i += NTH ) {
+            const int ww = i / ORI_NBINS, b = i - ww * ORI_NBINS;
             float s = 0.0f;
             #pragma unroll 8
-            for( int l = 0; l < 32; l++ ) s += col[wid][b][l];
+            for( int l = 0; l < 32; l++ ) s += col[ww][b][( l + b ) & 31];       /* rotated start: no bank conflict, still a fixed order */
+            part[ww][b] = s;
+        }
+        __syncthreads();
+        if( wid != 0 ) continue;            /* the rest is a warp's worth of work; the others wait at the next hand-out */
+        for( int b = lane; b < ORI_NBINS; b += 32 ) {
+            float s = 0.0f;
+            #pragma unroll
+            for( int ww = 0; ww < ORI_WARPS; ww++ ) s += part[ww][b];
             hist[wid][b] = s;
         }
         __syncwarp();

@@ -330,7 +330,7 @@ static int run_frame( psift_ctx* c, Slot& s )
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
     CU( cudaEventRecord( s.ev[3], st ) );
-    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, 148 * 5, st, &c->launches ) );
+    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, 148 * 10, st, &c->launches ) );
     CU( cudaEventRecord( s.ev[4], st ) );
     CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.lintex_d, c->d_dt, s.desc, s.feat, 148 * 4, st, &c->launches ) );
     CU( cudaEventRecord( s.ev[5], st ) );
