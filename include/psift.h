@@ -110,7 +110,10 @@ void psift_destroy( psift_ctx* ctx );                               /* PopSift::
 
 /* PopSift::enqueue (popsift.cpp:139-169) + the worker's step1/step2/get_descriptors
  * (popsift.cpp:182-213).  The image is copied before the call returns (popsift.cpp:245-247).
- * The work is queued on the context's streams; psift_wait blocks until the features are on the host. */
+ * The work is queued on the context's streams; psift_wait blocks until the features are on the host.  A frame
+ * with more keypoints than the slot's buffers hold (they start at max_extrema, sift_pyramid.cu:148-159) is re-run
+ * inside psift_wait with larger buffers (Pyramid::reallocExtrema, sift_pyramid.cu:179-215): a caller-owned device
+ * image therefore has to stay valid until psift_wait returns. */
 int  psift_submit_u8 ( psift_ctx* ctx, int w, int h, const uint8_t* host, size_t pitch_bytes, psift_job** out );
 int  psift_submit_f32( psift_ctx* ctx, int w, int h, const float*   host, size_t pitch_bytes, psift_job** out );
 /* same, input already resident in device memory (no H2D inside) */

@@ -350,9 +350,10 @@ __global__ void k_extrema_finish( Counters* ct, int n_oct, int max_extrema, int 
 {
     pdl_enter();
     if( threadIdx.x != 0 || blockIdx.x != 0 ) return;
-    int ps = 0;
+    int ps = 0, need = 0;
     for( int o = 0; o < MAX_OCT; o++ ) {
         int c = ( o < n_oct ) ? min( ct->ext_ct[o], max_extrema ) : 0;
+        need += c;
         if( ps + c > ext_capacity ) { c = max( 0, ext_capacity - ps ); ct->overflow = 1; }
         ct->ext_ct[o] = c;
         ct->ext_ps[o] = ps;
@@ -360,6 +361,7 @@ __global__ void k_extrema_finish( Counters* ct, int n_oct, int max_extrema, int 
     }
     ct->ext_ps[MAX_OCT] = ps;
     ct->ext_total = ps;
+    ct->need_ext = need;
 }
 
 /* Deterministic order: rank every candidate of an octave by its detection voxel

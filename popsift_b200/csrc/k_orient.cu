@@ -236,6 +236,7 @@ k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* 
     if( threadIdx.x == 0 ) {
         const int ori_total = min( carry, desc_capacity );
         ct->ori_total = ori_total;
+        ct->need_desc = carry;
         for( int o = 0; o < MAX_OCT; o++ ) {
             const int fe = ct->ext_ps[o], n = ct->ext_ct[o];
             int lo = ori_total, hi = ori_total;

@@ -267,6 +267,23 @@ static int bind_input_texture( Slot& s, const void* dptr, size_t pitch, int w, i
     return PSIFT_OK;
 }
 
+/* Buffers sized by the number of keypoints / descriptors of a frame.  The reference starts from the same sizes
+ * (max_extrema total, sift_pyramid.cu:148-159) and reallocates when a frame needs more
+ * (Pyramid::reallocExtrema, sift_pyramid.cu:179-215); psift_wait() does the same and re-runs the frame. */
+static int alloc_keypoint_buffers( Slot& s, int ext_cap, int desc_cap )
+{
+    cudaFree( s.sorted ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.filt );
+    s.sorted = nullptr; s.ext = nullptr; s.feat = nullptr; s.desc_map = nullptr; s.desc = nullptr; s.filt = nullptr;
+    s.ext_cap = ext_cap; s.desc_cap = desc_cap;
+    CU( cudaMalloc( &s.sorted, sizeof(Cand) * (size_t)ext_cap ) );
+    CU( cudaMalloc( &s.ext,    sizeof(psift_extremum) * (size_t)ext_cap ) );
+    CU( cudaMalloc( &s.feat,   sizeof(psift_feature) * (size_t)ext_cap ) );
+    CU( cudaMalloc( &s.desc_map, sizeof(int) * (size_t)desc_cap ) );
+    CU( cudaMalloc( &s.desc,   sizeof(float) * 128 * (size_t)desc_cap ) );
+    CU( cudaMalloc( &s.filt, filter_scratch_bytes( ext_cap ) ) );
+    return PSIFT_OK;
+}
+
 static int init_slot( psift_ctx* c, Slot& s )
 {
     CU( cudaStreamCreateWithFlags( &s.stream, cudaStreamNonBlocking ) );
@@ -282,16 +299,10 @@ static int init_slot( psift_ctx* c, Slot& s )
     }
     const int me = c->cfg.max_extrema;
     s.cand_stride = me;
-    s.ext_cap  = me;                                     /* sift_pyramid.cu:148-151 */
-    s.desc_cap = std::max( 2 * me, me + me / 4 );          /* sift_pyramid.cu:153-159 */
     CU( cudaMalloc( &s.cand,   sizeof(Cand) * (size_t)me * MAX_OCT ) );
-    CU( cudaMalloc( &s.sorted, sizeof(Cand) * (size_t)s.ext_cap ) );
-    CU( cudaMalloc( &s.ext,    sizeof(psift_extremum) * (size_t)s.ext_cap ) );
-    CU( cudaMalloc( &s.feat,   sizeof(psift_feature) * (size_t)s.ext_cap ) );
-    CU( cudaMalloc( &s.desc_map, sizeof(int) * (size_t)s.desc_cap ) );
-    CU( cudaMalloc( &s.desc,   sizeof(float) * 128 * (size_t)s.desc_cap ) );
+    int rc = alloc_keypoint_buffers( s, me, std::max( 2 * me, me + me / 4 ) );   /* sift_pyramid.cu:148-159 */
+    if( rc ) return rc;
     CU( cudaMalloc( &s.ct, sizeof(Counters) ) );
-    CU( cudaMalloc( &s.filt, filter_scratch_bytes( s.ext_cap ) ) );
     CU( cudaMallocHost( &s.h_ct, sizeof(Counters) ) );
     return PSIFT_OK;
 }
@@ -651,6 +662,19 @@ int psift_wait( psift_job* j, psift_result* r )
     CU( cudaSetDevice( c->device ) );
     if( !j->waited ) {
         CU( cudaEventSynchronize( s.ev_counters ) );
+        /* a frame with more keypoints than the buffers hold: grow them and run it again (the input texture, or the
+         * seed plane in the arena, is still in place; a caller-owned device image must stay valid until here).  A
+         * clamped keypoint list under-counts the descriptors, hence the loop. */
+        for( int pass = 0; s.h_ct->overflow && pass < 4; pass++ ) {
+            const int ne = std::max( s.ext_cap,  s.h_ct->need_ext  + s.h_ct->need_ext / 8 );
+            const int nd = std::max( std::max( s.desc_cap, s.h_ct->need_desc + s.h_ct->need_desc / 4 ), ne + ne / 4 );
+            CU( cudaStreamSynchronize( s.stream ) );
+            int rc = alloc_keypoint_buffers( s, ne, nd );
+            if( rc ) return rc;
+            rc = run_frame( c, s );
+            if( rc ) return rc;
+            CU( cudaEventSynchronize( s.ev_counters ) );
+        }
         const int n_ext = s.h_ct->ext_total, n_desc = s.h_ct->ori_total;
         int rc = ensure_host_results( s, n_ext, n_desc );
         if( rc ) return rc;

@@ -246,6 +246,25 @@ def test_banded_equals_whole(w, h, parts, seed_px, flags):
     assert da == db
 
 
+def test_keypoint_buffers_grow():
+    """A frame with more keypoints than the buffers were sized for (max_extrema in total, sift_pyramid.cu:148-159)
+    is re-run with larger buffers, like Pyramid::reallocExtrema (sift_pyramid.cu:179-215): the result equals that of
+    a context whose buffers were large from the start.  max_extrema still bounds every single octave."""
+    img = synth.gen(640, 480, 5)
+    big = capi.default_config()
+    with capi.Context(big) as ctx:
+        want = ctx.extract(img)
+    per_oct = int(max(want.ext_ct))
+    assert want.n_feat > per_oct + 8
+    small = capi.default_config(); small.max_extrema = per_oct + 1        # no octave is clamped, the total overflows
+    with capi.Context(small) as ctx:
+        got = ctx.extract(img)
+        again = ctx.extract(img)                                            # buffers stay grown: one pass
+    for r in (got, again):
+        assert r.n_feat == want.n_feat and r.n_desc == want.n_desc
+        assert np.array_equal(r.feat, want.feat) and np.array_equal(r.desc, want.desc)
+
+
 def test_popsift_demo_cli(tmp_path):
     """The reference's command line (src/application/main.cpp) on a P5 and a P6 file: output-features.txt holds one
     line per descriptor, `x y 1/s^2 0 1/s^2 d0..d127` (features.cu:308-328), and matches the golden run."""
