@@ -7,6 +7,8 @@
 #include "sift_constants.h"
 #include "sift_extremum.h"
 
+struct psift_dev_features;   /* psift.h: the C-ABI object behind FeaturesDev */
+
 namespace popsift {
 
 struct Feature
@@ -70,13 +72,37 @@ typedef FeaturesHost Features;
 
 std::ostream& operator<<( std::ostream& ostr, const FeaturesHost& feature );
 
-/* Device-resident results (reference features.h:100-118) belong to the matching mode, which is
- * outside the extraction path; the class exists so that code naming the type compiles. */
+/* Device-resident results of the matching mode (reference features.h:100-118, features.cu:126-302).  The three
+ * pointers are DEVICE memory on device getDevice(); Feature::desc[] of the device records point into the device
+ * descriptor block.  match() prints one accept/reject line per descriptor like the reference; matchTo() returns the
+ * same result as data. */
 class FeaturesDev : public FeaturesBase
 {
+    ::psift_dev_features* _handle;
+    Feature*     _ext;
+    Descriptor*  _ori;
+    int*         _rev; // the reverse map from descriptors to extrema
+    int          _device;
+
+    FeaturesDev( const FeaturesDev& );
+    FeaturesDev& operator=( const FeaturesDev& );
 public:
-    FeaturesDev( ) { }
-    virtual ~FeaturesDev( ) { }
+    struct Match { int best; int second; int accept; float dist_best; float dist_second; };
+
+    FeaturesDev( );
+    FeaturesDev( int num_ext, int num_ori );
+    explicit FeaturesDev( ::psift_dev_features* handle );   /* takes ownership (psift_wait_dev) */
+    virtual ~FeaturesDev( );
+
+    void reset( int num_ext, int num_ori );
+
+    void match( FeaturesDev* other );
+    std::vector<Match> matchTo( FeaturesDev* other );            /* extension */
+
+    inline Feature*    getFeatures()    { return _ext; }
+    inline Descriptor* getDescriptors() { return _ori; }
+    inline int*        getReverseMap()  { return _rev; }
+    inline int         getDevice() const { return _device; }     /* extension */
 };
 
 } // namespace popsift

@@ -25,7 +25,7 @@ struct PopSiftImpl;
 class SiftJob
 {
     std::promise<popsift::FeaturesBase*> _p;
-    std::future <popsift::FeaturesBase*> _f;
+    std::shared_future<popsift::FeaturesBase*> _f;   /* shared: get()/getDev()/getBase() may be called more than once */
     int                 _w;
     int                 _h;
     unsigned char*      _imageData;     /* private copy, byte or float pixels */

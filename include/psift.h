@@ -121,6 +121,34 @@ int  psift_submit_dev_u8( psift_ctx* ctx, int w, int h, const uint8_t* dev, size
 int  psift_wait( psift_job* job, psift_result* out );               /* SiftJob::get, popsift.cpp:300-313 */
 void psift_job_free( psift_job* job );                              /* delete SiftJob */
 
+/* ---- Device-resident results and matching (reference Config::MatchingMode) ----------------------------------
+ * psift_wait_dev replaces PopSift::matchPrepareLoop + Pyramid::clone_device_descriptors (popsift.cpp:215-236,
+ * sift_pyramid.cu:323-361): the job's features, descriptors and descriptor->feature map are cloned into device
+ * buffers owned by the returned object; nothing is copied to the host.  May be called instead of, or in addition
+ * to, psift_wait; the job is still released with psift_job_free.  psift_dev_features_alloc/free are FeaturesDev's
+ * constructor and destructor (features.cu:126-161).
+ * psift_match replaces FeaturesDev::match's compute_distance (features.cu:163-225, 268-302): for every left
+ * descriptor, match3[3*i+0..2] = {index of the nearest right descriptor, index of the second nearest, accept}, accept
+ * = d1/d2 < 0.8 on SQUARED L2 distances; dist2[2*i+0..1] = {d1, d2} (may be NULL).  Bit-identical to the reference's
+ * arithmetic, so the integers agree exactly.  Operands on different GPUs: the right one is copied over. */
+typedef struct psift_dev_features psift_dev_features;
+typedef struct psift_dev_info {
+    int            device, n_feat, n_desc;
+    psift_feature* feat;        /* device: n_feat records with descriptor indices */
+    void*          feat_ref;    /* device: n_feat popsift::Feature records (72 bytes, device Descriptor pointers, features.h:22-35) */
+    float*         desc;        /* device: n_desc x 128 */
+    int*           rev;         /* device: descriptor -> feature index (FeaturesDev::getReverseMap) */
+} psift_dev_info;
+int  psift_wait_dev( psift_job* job, psift_dev_features** out );
+int  psift_dev_features_alloc( int device, int n_feat, int n_desc, psift_dev_features** out );
+void psift_dev_features_free( psift_dev_features* f );
+int  psift_dev_features_info( const psift_dev_features* f, psift_dev_info* info );
+int  psift_match( const psift_dev_features* l, const psift_dev_features* r, int* match3_host, float* dist2_host );
+int  psift_match_dev( int device, const float* l_desc_dev, int l_len, const float* r_desc_dev, int r_len,
+                      int* match3_host, float* dist2_host );
+int  psift_dev_download( int device, const void* dev, void* host, size_t bytes );
+int  psift_dev_upload( int device, void* dev, const void* host, size_t bytes );
+
 /* Parity / profiling hooks (the reference's LogMode::All dumps, sift_octave.cu:110-187). Valid after
  * psift_wait and before the next submit on the same context slot. */
 int  psift_octave_size( psift_ctx* ctx, int octave, int* w, int* h );

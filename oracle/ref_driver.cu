@@ -36,6 +36,7 @@
 
 using namespace popsift;
 
+namespace popsift { __global__ void compute_distance( int3* match_matrix, Descriptor* l, int l_len, Descriptor* r, int r_len ); }
 namespace popsift { __global__ void ori_par( const int octave, const int ext_ct_prefix_sum, cudaTextureObject_t layer, const int w, const int h ); }
 
 static void die( const char* msg ) { fprintf( stderr, "ref_driver: %s\n", msg ); exit( 2 ); }
@@ -120,6 +121,31 @@ static void write_planes( const std::string& fn, Pyramid* pyr )
     fclose( f );
 }
 
+/* --match-desc L.f32 R.f32 --out X : the reference's matcher kernel (features.cu:184-225, what FeaturesDev::match
+ * launches, features.cu:268-285) on two raw descriptor files; writes l_len x int3 {best, second, accept} to X. */
+static int match_mode( const std::string& lf, const std::string& rf, const std::string& out )
+{
+    std::vector<unsigned char> lb = read_file( lf ), rb = read_file( rf );
+    const int nl = (int)( lb.size() / sizeof(Descriptor) ), nr = (int)( rb.size() / sizeof(Descriptor) );
+    FeaturesDev L( 1, std::max( nl, 1 ) ), R( 1, std::max( nr, 1 ) );
+    cudaMemcpy( L.getDescriptors(), lb.data(), (size_t)nl * sizeof(Descriptor), cudaMemcpyHostToDevice );
+    cudaMemcpy( R.getDescriptors(), rb.data(), (size_t)nr * sizeof(Descriptor), cudaMemcpyHostToDevice );
+    int3* mm = 0; cudaMalloc( &mm, sizeof(int3) * std::max( nl, 1 ) );
+    auto t0 = std::chrono::steady_clock::now();
+    if( nl > 0 ) compute_distance<<< dim3( nl ), dim3( 32 ) >>>( mm, L.getDescriptors(), nl, R.getDescriptors(), nr );
+    if( cudaDeviceSynchronize() != cudaSuccess ) die( "compute_distance failed" );
+    const double ms = std::chrono::duration<double, std::milli>( std::chrono::steady_clock::now() - t0 ).count();
+    std::vector<int3> h( std::max( nl, 1 ) );
+    cudaMemcpy( h.data(), mm, sizeof(int3) * nl, cudaMemcpyDeviceToHost );
+    FILE* f = fopen( out.c_str(), "wb" );
+    if( !f ) die( "cannot open match output" );
+    fwrite( h.data(), sizeof(int3), nl, f );
+    fclose( f );
+    cudaFree( mm );
+    printf( "{\"l_len\": %d, \"r_len\": %d, \"ms\": %.3f}\n", nl, nr, ms );
+    return 0;
+}
+
 int main( int argc, char** argv )
 {
     std::vector<std::string> inputs;
@@ -129,11 +155,13 @@ int main( int argc, char** argv )
 
     cudaSetDevice( 0 );
     Config conf;
+    std::string match_l, match_r;
 
     for( int i = 1; i < argc; i++ ) {
         std::string a = argv[i];
         auto next = [&]() -> const char* { if( i + 1 >= argc ) die( "missing value" ); return argv[++i]; };
         if(      a == "--in" )      inputs.push_back( next() );
+        else if( a == "--match-desc" ) { match_l = next(); match_r = next(); }
         else if( a == "--out" )     out_prefix = next();
         else if( a == "--w" )       w = atoi( next() );
         else if( a == "--h" )       h = atoi( next() );
@@ -167,6 +195,7 @@ int main( int argc, char** argv )
         else if( a == "--filter-sort" )  conf.setFilterSorting( std::string( next() ) );
         else { fprintf( stderr, "ref_driver: unknown flag %s\n", a.c_str() ); return 2; }
     }
+    if( !match_l.empty() ) return match_mode( match_l, match_r, out_prefix );
     if( inputs.empty() || w <= 0 || h <= 0 ) die( "need --in FILE --w W --h H" );
 
     /* PopSift::configure, reference popsift.cpp:63-87 */

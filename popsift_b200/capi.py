@@ -41,12 +41,20 @@ DESC = {"loop": 0, "iloop": 1, "grid": 2, "igrid": 3, "notile": 4}
 NORM = {"RootSift": 0, "classic": 1}
 FSORT = {"random": 0, "down": 1, "up": 2}   # reference sift_conf.cu:131-141 (up = smallest scale first)
 
+class DevInfo(C.Structure):
+    """psift_dev_info (psift.h)"""
+    _fields_ = [("device", C.c_int), ("n_feat", C.c_int), ("n_desc", C.c_int),
+                ("feat", C.c_void_p), ("feat_ref", C.c_void_p), ("desc", C.c_void_p), ("rev", C.c_void_p)]
+
+
 EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "psift_create", "psift_configure",
            "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_wait",
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
            "psift_launch_count", "psift_debug_mark", "psift_debug_mark_elapsed",
-           "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32"]
+           "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32",
+           "psift_wait_dev", "psift_dev_features_alloc", "psift_dev_features_free", "psift_dev_features_info", "psift_match",
+           "psift_match_dev", "psift_dev_download", "psift_dev_upload"]
 
 _lib = None
 
@@ -81,6 +89,14 @@ def lib():
         L.psift_band_seed_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int]
         L.psift_submit_seed_dev_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.psift_debug_mark.argtypes = [C.c_void_p, C.c_int]
+        L.psift_wait_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.psift_dev_features_alloc.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.psift_dev_features_free.argtypes = [C.c_void_p]
+        L.psift_dev_features_info.argtypes = [C.c_void_p, C.POINTER(DevInfo)]
+        L.psift_match.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.psift_match_dev.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.psift_dev_download.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.psift_dev_upload.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
         L.psift_debug_mark_elapsed.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         _lib = L
     return _lib
@@ -209,6 +225,19 @@ class Context:
     def free(self, job):
         lib().psift_job_free(job)
 
+    def wait_dev(self, job):
+        """device-resident result of a job (reference MatchingMode): a DevFeatures"""
+        h = C.c_void_p()
+        _chk(lib().psift_wait_dev(job, C.byref(h)))
+        return DevFeatures(h)
+
+    def extract_dev(self, img):
+        job = self.submit(img)
+        try:
+            return self.wait_dev(job)
+        finally:
+            self.free(job)
+
     def extract(self, img):
         job = self.submit(img)
         try:
@@ -271,3 +300,47 @@ def geometry(cfg, w, h):
     a, b, n = C.c_int(), C.c_int(), C.c_int()
     _chk(lib().psift_pyramid_geometry(C.byref(cfg), w, h, C.byref(a), C.byref(b), C.byref(n)))
     return a.value, b.value, n.value
+
+
+class DevFeatures:
+    """psift_dev_features: features, descriptors and the descriptor->feature map of one image in device memory
+    (reference FeaturesDev, features.h:100-118)."""
+    def __init__(self, handle):
+        self._h = handle
+        self.info = DevInfo()
+        _chk(lib().psift_dev_features_info(self._h, C.byref(self.info)))
+        self.n_feat, self.n_desc, self.device = self.info.n_feat, self.info.n_desc, self.info.device
+
+    @classmethod
+    def from_host(cls, desc, device=0):
+        """upload an (n,128) float32 array as a descriptor set (no features)"""
+        desc = np.ascontiguousarray(desc, np.float32).reshape(-1, 128)
+        h = C.c_void_p()
+        _chk(lib().psift_dev_features_alloc(device, 0, len(desc), C.byref(h)))
+        f = cls(h)
+        _chk(lib().psift_dev_upload(device, f.info.desc, desc.ctypes.data, desc.nbytes))
+        return f
+
+    def _download(self, ptr, shape, dtype):
+        out = np.empty(shape, dtype)
+        _chk(lib().psift_dev_download(self.device, ptr, out.ctypes.data, out.nbytes))
+        return out
+
+    def descriptors(self): return self._download(self.info.desc, (self.n_desc, 128), np.float32)
+    def features(self):    return self._download(self.info.feat, (self.n_feat,), FEATURE_DTYPE)
+    def reverse_map(self): return self._download(self.info.rev, (self.n_desc,), np.int32)
+    def features_ref_layout(self): return self._download(self.info.feat_ref, (self.n_feat, 72), np.uint8)
+
+    def match(self, other):
+        """FeaturesDev::match (features.cu:268-302): (match[n,3] int32 = best, second, accept; dist[n,2] = squared L2)"""
+        m = np.zeros((self.n_desc, 3), np.int32); d = np.zeros((self.n_desc, 2), np.float32)
+        _chk(lib().psift_match(self._h, other._h, m.ctypes.data, d.ctypes.data))
+        return m, d
+
+    def close(self):
+        if self._h: lib().psift_dev_features_free(self._h); self._h = None
+    def __enter__(self): return self
+    def __exit__(self, *a): self.close()
+    def __del__(self):
+        try: self.close()
+        except Exception: pass

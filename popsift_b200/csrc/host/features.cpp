@@ -1,5 +1,8 @@
-/* Feature / FeaturesHost (reference src/popsift/features.cu:20-110, 308-336). */
+/* Feature / FeaturesHost / FeaturesDev (reference src/popsift/features.cu:20-110, 126-302, 308-336). */
 #include <popsift/features.h>
+#include <psift.h>
+#include <cstdio>
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <iomanip>
@@ -47,6 +50,68 @@ std::ostream& operator<<( std::ostream& ostr, const FeaturesHost& feature )
 {
     feature.print( ostr, false );
     return ostr;
+}
+
+/* ------------------------------------------------------------------ FeaturesDev */
+
+FeaturesDev::FeaturesDev( ) : _handle( 0 ), _ext( 0 ), _ori( 0 ), _rev( 0 ), _device( 0 ) { }
+FeaturesDev::FeaturesDev( int num_ext, int num_ori ) : _handle( 0 ), _ext( 0 ), _ori( 0 ), _rev( 0 ), _device( 0 ) { reset( num_ext, num_ori ); }
+
+FeaturesDev::FeaturesDev( psift_dev_features* handle ) : _handle( handle ), _ext( 0 ), _ori( 0 ), _rev( 0 ), _device( 0 )
+{
+    psift_dev_info info;
+    if( handle && psift_dev_features_info( handle, &info ) == PSIFT_OK ) {
+        _ext = (Feature*)info.feat_ref; _ori = (Descriptor*)info.desc; _rev = info.rev; _device = info.device;
+        setFeatureCount( info.n_feat );
+        setDescriptorCount( info.n_desc );
+    }
+}
+
+FeaturesDev::~FeaturesDev( ) { psift_dev_features_free( _handle ); }
+
+void FeaturesDev::reset( int num_ext, int num_ori )
+{
+    psift_dev_features_free( _handle );
+    _handle = 0; _ext = 0; _ori = 0; _rev = 0;
+    setFeatureCount( 0 ); setDescriptorCount( 0 );
+    psift_dev_info info;
+    if( psift_dev_features_alloc( _device, num_ext, num_ori, &_handle ) != PSIFT_OK || psift_dev_features_info( _handle, &info ) != PSIFT_OK ) {
+        std::cerr << "popsift: failed to allocate device memory for " << num_ext << " features / " << num_ori << " descriptors: "
+                  << psift_last_error() << std::endl;
+        return;
+    }
+    _ext = (Feature*)info.feat_ref; _ori = (Descriptor*)info.desc; _rev = info.rev;
+    setFeatureCount( num_ext );
+    setDescriptorCount( num_ori );
+}
+
+std::vector<FeaturesDev::Match> FeaturesDev::matchTo( FeaturesDev* other )
+{
+    std::vector<Match> out;
+    const int n = getDescriptorCount();
+    if( !other || !_handle || !other->_handle || n <= 0 ) return out;
+    std::vector<int> m( 3 * (size_t)n ); std::vector<float> d( 2 * (size_t)n );
+    if( psift_match( _handle, other->_handle, m.data(), d.data() ) != PSIFT_OK ) {
+        std::cerr << "popsift: match failed: " << psift_last_error() << std::endl;
+        return out;
+    }
+    out.resize( n );
+    for( int i = 0; i < n; i++ ) { out[i].best = m[3 * i]; out[i].second = m[3 * i + 1]; out[i].accept = m[3 * i + 2]; out[i].dist_best = d[2 * i]; out[i].dist_second = d[2 * i + 1]; }
+    return out;
+}
+
+/* the reference prints from a device kernel (show_distance, features.cu:227-266); same text, from the host */
+void FeaturesDev::match( FeaturesDev* other )
+{
+    const std::vector<Match> m = matchTo( other );
+    if( m.empty() ) return;
+    std::vector<int> lf( getDescriptorCount() ), rf( std::max( other->getDescriptorCount(), 1 ) );
+    psift_dev_download( _device, _rev, lf.data(), sizeof(int) * lf.size() );
+    psift_dev_download( other->_device, other->_rev, rf.data(), sizeof(int) * (size_t)other->getDescriptorCount() );
+    for( size_t i = 0; i < m.size(); i++ )
+        printf( "%s feat %4d [%4d] matches feat %4d [%4d] ( 2nd feat %4d [%4d] ) dist %.3f vs %.3f\n",
+                m[i].accept ? "accept" : "reject", lf[i], (int)i, rf[m[i].best], m[i].best, rf[m[i].second], m[i].second,
+                m[i].dist_best, m[i].dist_second );
 }
 
 /* "x y 1/sigma^2 0 1/sigma^2 d0 ... d127", one line per orientation (features.cu:308-328) */

@@ -28,7 +28,7 @@ using popsift::FeaturesBase;
 SiftJob::SiftJob( int w, int h, const unsigned char* imageData )
     : _w( w ), _h( h ), _imageData( 0 ), _is_float( false ), _img( 0 )
 {
-    _f = _p.get_future();
+    _f = _p.get_future().share();
     const size_t n = (size_t)w * h;
     _imageData = (unsigned char*)malloc( n ? n : 1 );
     if( _imageData ) memcpy( _imageData, imageData, n );
@@ -38,7 +38,7 @@ SiftJob::SiftJob( int w, int h, const unsigned char* imageData )
 SiftJob::SiftJob( int w, int h, const float* imageData )
     : _w( w ), _h( h ), _imageData( 0 ), _is_float( true ), _img( 0 )
 {
-    _f = _p.get_future();
+    _f = _p.get_future().share();
     const size_t n = (size_t)w * h * sizeof(float);
     _imageData = (unsigned char*)malloc( n ? n : 1 );
     if( _imageData ) memcpy( _imageData, imageData, n );
@@ -70,6 +70,7 @@ struct PopSiftImpl
     std::vector<psift_ctx*> ctx;
     std::vector<std::thread> workers;
     psift_config            cfg;
+    bool                    matching = false;              /* Config::MatchingMode: results stay on the device */
     static const int        IN_FLIGHT = 3;
 
     void worker( int idx );
@@ -115,7 +116,7 @@ void PopSiftImpl::worker( int idx )
                                     : psift_submit_u8 ( c, job->width(), job->height(), job->data(), 0, &pj );
             if( rc != PSIFT_OK ) {
                 std::cerr << "popsift: extraction failed: " << psift_last_error() << std::endl;
-                job->setFeatures( new FeaturesHost( 0, 0 ) );
+                job->setFeatures( matching ? (FeaturesBase*)new popsift::FeaturesDev( ) : (FeaturesBase*)new FeaturesHost( 0, 0 ) );
                 continue;
             }
             inflight.push_back( std::make_pair( job, pj ) );
@@ -129,8 +130,16 @@ void PopSiftImpl::worker( int idx )
         SiftJob* job = inflight.front().first; psift_job* pj = inflight.front().second;
         inflight.pop_front();
         psift_result r;
-        FeaturesHost* fh;
-        if( psift_wait( pj, &r ) == PSIFT_OK ) {
+        FeaturesBase* fh;
+        if( matching ) {
+            /* matchPrepareLoop, popsift.cpp:215-236: clone on the device, nothing goes to the host */
+            psift_dev_features* df = 0;
+            if( psift_wait_dev( pj, &df ) == PSIFT_OK ) fh = new popsift::FeaturesDev( df );
+            else {
+                std::cerr << "popsift: extraction failed: " << psift_last_error() << std::endl;
+                fh = new popsift::FeaturesDev( );
+            }
+        } else if( psift_wait( pj, &r ) == PSIFT_OK ) {
             fh = convert( r );
             if( r.n_desc == 0 && r.n_feat != 0 ) std::cerr << "Warning: no descriptors extracted" << std::endl;
         } else {
@@ -154,8 +163,7 @@ PopSift::PopSift( ImageMode imode )
 PopSift::PopSift( const popsift::Config& config, popsift::Config::ProcessingMode mode, ImageMode imode )
     : _impl( new PopSiftImpl ), _last_init_w( 0 ), _last_init_h( 0 ), _image_mode( imode )
 {
-    if( mode == popsift::Config::MatchingMode )
-        std::cerr << "popsift: MatchingMode (device-resident features) is outside the extraction path; using ExtractingMode" << std::endl;
+    _impl->matching = ( mode == popsift::Config::MatchingMode );   /* popsift.cpp:26-36 */
     configure( config, true );
 }
 

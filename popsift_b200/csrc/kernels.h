@@ -24,6 +24,9 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
 size_t filter_scratch_bytes( int ext_capacity );
 cudaError_t launch_grid_filter( const PyrLayout& L, const psift_config& cfg, Cand* list, Cand* spare, int ext_capacity,
                                 Counters* ct, void* scratch, cudaStream_t st, long long* launches );
+/* k_match.cu */
+cudaError_t launch_match( const float* l, int l_len, const float* r, int r_len, int* out3, float* dist2, cudaStream_t st );
+cudaError_t launch_ref_features( const psift_feature* in, int n, float* desc_base, void* out72, cudaStream_t st );
 /* k_orient.cu */
 cudaError_t launch_orientation( const PyrLayout& L, const Cand* sorted, Counters* ct, psift_extremum* ext,
                                 int* desc_map, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches );

@@ -350,6 +350,25 @@ static int run_frame( psift_ctx* c, Slot& s )
     return PSIFT_OK;
 }
 
+/* Wait for a frame's counters.  A frame with more keypoints than the buffers hold: grow them and run it again (the
+ * input texture, or the seed plane in the arena, is still in place; a caller-owned device image must stay valid
+ * until here).  A clamped keypoint list under-counts the descriptors, hence the loop.  Idempotent. */
+static int settle_frame( psift_ctx* c, Slot& s )
+{
+    CU( cudaEventSynchronize( s.ev_counters ) );
+    for( int pass = 0; s.h_ct->overflow && pass < 4; pass++ ) {
+        const int ne = std::max( s.ext_cap,  s.h_ct->need_ext  + s.h_ct->need_ext / 8 );
+        const int nd = std::max( std::max( s.desc_cap, s.h_ct->need_desc + s.h_ct->need_desc / 4 ), ne + ne / 4 );
+        CU( cudaStreamSynchronize( s.stream ) );
+        int rc = alloc_keypoint_buffers( s, ne, nd );
+        if( rc ) return rc;
+        rc = run_frame( c, s );
+        if( rc ) return rc;
+        CU( cudaEventSynchronize( s.ev_counters ) );
+    }
+    return PSIFT_OK;
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /*                                           C ABI                                            */
 /* ------------------------------------------------------------------------------------------ */
@@ -661,20 +680,8 @@ int psift_wait( psift_job* j, psift_result* r )
     Slot& s = c->slots[j->slot];
     CU( cudaSetDevice( c->device ) );
     if( !j->waited ) {
-        CU( cudaEventSynchronize( s.ev_counters ) );
-        /* a frame with more keypoints than the buffers hold: grow them and run it again (the input texture, or the
-         * seed plane in the arena, is still in place; a caller-owned device image must stay valid until here).  A
-         * clamped keypoint list under-counts the descriptors, hence the loop. */
-        for( int pass = 0; s.h_ct->overflow && pass < 4; pass++ ) {
-            const int ne = std::max( s.ext_cap,  s.h_ct->need_ext  + s.h_ct->need_ext / 8 );
-            const int nd = std::max( std::max( s.desc_cap, s.h_ct->need_desc + s.h_ct->need_desc / 4 ), ne + ne / 4 );
-            CU( cudaStreamSynchronize( s.stream ) );
-            int rc = alloc_keypoint_buffers( s, ne, nd );
-            if( rc ) return rc;
-            rc = run_frame( c, s );
-            if( rc ) return rc;
-            CU( cudaEventSynchronize( s.ev_counters ) );
-        }
+        int rc0 = settle_frame( c, s );
+        if( rc0 ) return rc0;
         const int n_ext = s.h_ct->ext_total, n_desc = s.h_ct->ori_total;
         int rc = ensure_host_results( s, n_ext, n_desc );
         if( rc ) return rc;
@@ -783,6 +790,127 @@ int psift_debug_mark_elapsed( psift_ctx* c, float* ms )
     if( !c || !ms || !c->mark_stream ) return fail( PSIFT_E_INVALID, "no marks set" );
     CU( cudaEventSynchronize( c->mark_ev[1] ) );
     CU( cudaEventElapsedTime( ms, c->mark_ev[0], c->mark_ev[1] ) );
+    return PSIFT_OK;
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * Device-resident results and matching (reference Config::MatchingMode: popsift.cpp:215-236,
+ * Pyramid::clone_device_descriptors sift_pyramid.cu:323-361, FeaturesDev features.cu:126-302)
+ * ------------------------------------------------------------------------------------------- */
+} // extern "C"  (the struct below is C++)
+
+struct psift_dev_features {
+    int device = 0, n_feat = 0, n_desc = 0;
+    psift_feature* feat = nullptr;      /* n_feat records, descriptor INDICES */
+    void*  feat_ref = nullptr;          /* n_feat records in the reference's 72-byte layout, device descriptor POINTERS */
+    float* desc = nullptr;              /* n_desc x 128 */
+    int*   rev = nullptr;               /* descriptor -> feature (feat_to_ext_map) */
+};
+
+extern "C" {
+
+int psift_dev_features_alloc( int device, int n_feat, int n_desc, psift_dev_features** out )
+{
+    if( !out || n_feat < 0 || n_desc < 0 ) return fail( PSIFT_E_INVALID, "bad argument" );
+    *out = nullptr;
+    CU( cudaSetDevice( device ) );
+    psift_dev_features* f = new psift_dev_features;
+    f->device = device; f->n_feat = n_feat; f->n_desc = n_desc;
+    cudaError_t e = cudaMalloc( &f->feat, sizeof(psift_feature) * (size_t)std::max( n_feat, 1 ) );
+    if( e == cudaSuccess ) e = cudaMalloc( &f->feat_ref, (size_t)72 * std::max( n_feat, 1 ) );
+    if( e == cudaSuccess ) e = cudaMalloc( &f->desc, sizeof(float) * 128 * (size_t)std::max( n_desc, 1 ) );
+    if( e == cudaSuccess ) e = cudaMalloc( &f->rev, sizeof(int) * (size_t)std::max( n_desc, 1 ) );
+    if( e != cudaSuccess ) { psift_dev_features_free( f ); return fail( PSIFT_E_CUDA, "device features: %s", cudaGetErrorString( e ) ); }
+    *out = f;
+    return PSIFT_OK;
+}
+
+void psift_dev_features_free( psift_dev_features* f )
+{
+    if( !f ) return;
+    cudaSetDevice( f->device );
+    cudaFree( f->feat ); cudaFree( f->feat_ref ); cudaFree( f->desc ); cudaFree( f->rev );
+    delete f;
+}
+
+int psift_dev_features_info( const psift_dev_features* f, psift_dev_info* info )
+{
+    if( !f || !info ) return fail( PSIFT_E_INVALID, "null argument" );
+    info->device = f->device; info->n_feat = f->n_feat; info->n_desc = f->n_desc;
+    info->feat = f->feat; info->feat_ref = f->feat_ref; info->desc = f->desc; info->rev = f->rev;
+    return PSIFT_OK;
+}
+
+int psift_wait_dev( psift_job* j, psift_dev_features** out )
+{
+    if( !j || !out ) return fail( PSIFT_E_INVALID, "null argument" );
+    *out = nullptr;
+    psift_ctx* c = j->ctx;
+    Slot& s = c->slots[j->slot];
+    CU( cudaSetDevice( c->device ) );
+    int rc = settle_frame( c, s );
+    if( rc ) return rc;
+    const int n_ext = s.h_ct->ext_total, n_desc = s.h_ct->ori_total;
+    psift_dev_features* f = nullptr;
+    rc = psift_dev_features_alloc( c->device, n_ext, n_desc, &f );
+    if( rc ) return rc;
+    cudaError_t e = cudaSuccess;
+    if( n_ext > 0 ) e = cudaMemcpyAsync( f->feat, s.feat, sizeof(psift_feature) * (size_t)n_ext, cudaMemcpyDeviceToDevice, s.stream );
+    if( e == cudaSuccess && n_desc > 0 ) e = cudaMemcpyAsync( f->desc, s.desc, sizeof(float) * 128 * (size_t)n_desc, cudaMemcpyDeviceToDevice, s.stream );
+    if( e == cudaSuccess && n_desc > 0 ) e = cudaMemcpyAsync( f->rev, s.desc_map, sizeof(int) * (size_t)n_desc, cudaMemcpyDeviceToDevice, s.stream );
+    if( e == cudaSuccess ) e = launch_ref_features( f->feat, n_ext, f->desc, f->feat_ref, s.stream );
+    if( e == cudaSuccess ) e = cudaStreamSynchronize( s.stream );
+    if( e != cudaSuccess ) { psift_dev_features_free( f ); return fail( PSIFT_E_CUDA, "clone to device features: %s", cudaGetErrorString( e ) ); }
+    *out = f;
+    return PSIFT_OK;
+}
+
+int psift_match_dev( int device, const float* l_desc, int l_len, const float* r_desc, int r_len, int* match3, float* dist2 )
+{
+    if( l_len < 0 || r_len < 0 || ( l_len > 0 && ( !l_desc || !match3 ) ) || ( r_len > 0 && !r_desc ) ) return fail( PSIFT_E_INVALID, "bad argument" );
+    if( l_len == 0 ) return PSIFT_OK;
+    CU( cudaSetDevice( device ) );
+    int* d_m = nullptr; float* d_d = nullptr;
+    CU( cudaMalloc( &d_m, sizeof(int) * 3 * (size_t)l_len ) );
+    cudaError_t e = dist2 ? cudaMalloc( &d_d, sizeof(float) * 2 * (size_t)l_len ) : cudaSuccess;
+    if( e == cudaSuccess ) e = launch_match( l_desc, l_len, r_desc, r_len, d_m, d_d, 0 );
+    if( e == cudaSuccess ) e = cudaMemcpy( match3, d_m, sizeof(int) * 3 * (size_t)l_len, cudaMemcpyDeviceToHost );
+    if( e == cudaSuccess && dist2 ) e = cudaMemcpy( dist2, d_d, sizeof(float) * 2 * (size_t)l_len, cudaMemcpyDeviceToHost );
+    cudaFree( d_m ); cudaFree( d_d );
+    if( e != cudaSuccess ) return fail( PSIFT_E_CUDA, "match: %s", cudaGetErrorString( e ) );
+    return PSIFT_OK;
+}
+
+int psift_match( const psift_dev_features* l, const psift_dev_features* r, int* match3, float* dist2 )
+{
+    if( !l || !r ) return fail( PSIFT_E_INVALID, "null argument" );
+    if( l->device == r->device ) return psift_match_dev( l->device, l->desc, l->n_desc, r->desc, r->n_desc, match3, dist2 );
+    /* the right-hand descriptors live on another GPU: bring them over (NVLink peer copy) */
+    CU( cudaSetDevice( l->device ) );
+    float* tmp = nullptr;
+    CU( cudaMalloc( &tmp, sizeof(float) * 128 * (size_t)std::max( r->n_desc, 1 ) ) );
+    cudaError_t e = cudaMemcpyPeer( tmp, l->device, r->desc, r->device, sizeof(float) * 128 * (size_t)r->n_desc );
+    int rc = e == cudaSuccess ? psift_match_dev( l->device, l->desc, l->n_desc, tmp, r->n_desc, match3, dist2 )
+                              : fail( PSIFT_E_CUDA, "peer copy: %s", cudaGetErrorString( e ) );
+    cudaFree( tmp );
+    return rc;
+}
+
+int psift_dev_download( int device, const void* dev, void* host, size_t bytes )
+{
+    if( bytes == 0 ) return PSIFT_OK;
+    if( !dev || !host ) return fail( PSIFT_E_INVALID, "null argument" );
+    CU( cudaSetDevice( device ) );
+    CU( cudaMemcpy( host, dev, bytes, cudaMemcpyDeviceToHost ) );
+    return PSIFT_OK;
+}
+
+int psift_dev_upload( int device, void* dev, const void* host, size_t bytes )
+{
+    if( bytes == 0 ) return PSIFT_OK;
+    if( !dev || !host ) return fail( PSIFT_E_INVALID, "null argument" );
+    CU( cudaSetDevice( device ) );
+    CU( cudaMemcpy( dev, host, bytes, cudaMemcpyHostToDevice ) );
     return PSIFT_OK;
 }
 

@@ -59,6 +59,23 @@ CASES = {
 }
 
 
+# Matcher goldens (reference compute_distance, features.cu:184-225, run by `ref_driver --match-desc`): the left and
+# right descriptor sets are those of two golden extraction cases above; output tests/golden/ref/<name>.match.bin.
+MATCH_CASES = {
+    "m_g640_vs_filter":   ("g640_default", "g640_filter"),      # right is a subset of left: exact zeros
+    "m_g256_vs_opencv":   ("g256_default", "g256_opencv"),      # same image, other mode: near matches
+    "m_g256_vs_g640":     ("g256_default", "g640_default"),     # unrelated images
+    "m_g640_vs_g256":     ("g640_default", "g256_default"),
+    "m_g256_self":        ("g256_default", "g256_default"),
+    "m_check_self":       ("check_default", "check_default"),   # checkerboard: repeated descriptors, ties
+    "m_multi9_vs_l2":     ("g256_multi9", "g256_l2"),           # scaled descriptors
+    "m_tiny":             ("g17_default", "blob_default"),      # 2 x 3
+    "m_one_right":        ("g64_default", "g17_default"),       # r_len 2
+    "m_empty_right":      ("g64_default", "const_default"),     # r_len 0
+    "m_empty_left":       ("const_default", "g64_default"),     # l_len 0
+}
+
+
 def image_path(name):
     return os.path.join(GOLD, "inputs", name + ".u8")
 

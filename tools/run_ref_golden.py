@@ -26,4 +26,18 @@ for case, (img, flags, planes) in gc.CASES.items():
         print(case, "TIMEOUT", flush=True); log[case] = {"rc": -9}; continue
     log[case] = {"rc": r.returncode, "stdout": r.stdout.strip(), "stderr": r.stderr.strip()[-400:]}
     print(case, r.returncode, r.stdout.strip(), r.stderr.strip()[-200:], flush=True)
+# matcher goldens: descriptor sets come from the committed extraction goldens
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import refio
+for case, (lc, rc_) in gc.MATCH_CASES.items():
+    if only and case not in only:
+        continue
+    files = []
+    for c in (lc, rc_):
+        fn = os.path.join(OUT, "_desc_" + c + ".f32")
+        refio.RefFeatures(os.path.join(refio.GOLD, "ref", c + ".feat.bin")).desc.astype("<f4").tofile(fn)
+        files.append(fn)
+    r = subprocess.run([drv, "--match-desc", files[0], files[1], "--out", os.path.join(OUT, case + ".match.bin")], capture_output=True, text=True, timeout=60)
+    log[case] = {"rc": r.returncode, "stdout": r.stdout.strip(), "stderr": r.stderr.strip()[-400:]}
+    print(case, r.returncode, r.stdout.strip(), r.stderr.strip()[-200:], flush=True)
 json.dump(log, open(os.path.join(OUT, "log.json"), "w"), indent=1)
