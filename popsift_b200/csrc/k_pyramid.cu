@@ -479,12 +479,110 @@ static cudaError_t launch_blur( const BlurArgs& a, cudaStream_t st )
 
 /* Build every Gaussian level of every octave (reference Pyramid::build_pyramid,
  * s_pyramid_build.cu:460-596, default branch :549-577). */
-cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, int gauss_mode,
+
+/* ------------------------------------------------------------------------------------------ */
+/* Fixed9 / Fixed15 (reference s_pyramid_fixed.cu, K8): every level is filtered in ONE step from a fixed source
+ * -- the input image for octave 0 (relativeTexAddress::octave_fixed, :127-186, tables abs_o0, result x255), level 0
+ * of the same octave otherwise (absoluteTexAddress::octave_fixed, :66-119, tables abs_oN) -- with exactly S = 4 or 7
+ * one-sided taps, VERTICAL pass first (:49-64, :131-147), then the horizontal one (the reference's warp shuffles,
+ * :23-43, are just reads of the neighbouring columns' vertical results).  Accumulation order as compiled in the
+ * reference build (SASS of oracle/_ref/obj/s_pyramid_fixed.o), both passes:
+ *     acc = fma(centre, g0, pair1*g1);  acc = fma(pair_i, g_i, acc)  for i = 2..S;      pair_i = v(-i) + v(+i)
+ * and the texture rows are fma(1/h, -+i, ypos).  Not a fast path: a 64x16 tile, vertical results of tile + 2S columns in
+ * shared memory. */
+struct FixedArgs {
+    const float* src; cudaTextureObject_t tex; float* dst; float* ds_dst;
+    int w, h, pitch, ds_pitch; float tshift;
+    float g[8];
+};
+constexpr int FXW = 64, FXH = 16;
+
+template<int S, bool FROM_TEX>
+__global__ void __launch_bounds__( 256 )
+k_fixed_level( const FixedArgs a )
+{
+    __shared__ float V[FXH][FXW + 2 * S];
+    pdl_enter();
+    const int x0 = blockIdx.x * FXW, y0 = blockIdx.y * FXH;
+    const float mul_w = __frcp_rn( (float)a.w ), mul_h = __frcp_rn( (float)a.h );
+    for( int q = threadIdx.x; q < FXH * ( FXW + 2 * S ); q += 256 ) {
+        const int r = q / ( FXW + 2 * S ), cc = q - r * ( FXW + 2 * S );
+        const int c = x0 - S + cc, y = y0 + r;
+        float acc = 0.0f;
+        if( y < a.h ) {
+            float ctr, pr[S + 1];
+            if( FROM_TEX ) {
+                const float xpos = __fmul_rn( __fadd_rn( (float)c, a.tshift ), mul_w );
+                const float ypos = __fmul_rn( __fadd_rn( (float)y, a.tshift ), mul_h );
+                ctr = tex2D<float>( a.tex, xpos, ypos );
+#pragma unroll
+                for( int i = 1; i <= S; i++ )
+                    pr[i] = __fadd_rn( tex2D<float>( a.tex, xpos, __fmaf_rn( mul_h, -(float)i, ypos ) ),
+                                       tex2D<float>( a.tex, xpos, __fmaf_rn( mul_h,  (float)i, ypos ) ) );
+            } else {
+                const int cx = min( max( c, 0 ), a.w - 1 );
+                ctr = a.src[(size_t)y * a.pitch + cx];
+#pragma unroll
+                for( int i = 1; i <= S; i++ )
+                    pr[i] = __fadd_rn( a.src[(size_t)max( y - i, 0 ) * a.pitch + cx], a.src[(size_t)min( y + i, a.h - 1 ) * a.pitch + cx] );
+            }
+            acc = __fmaf_rn( ctr, a.g[0], __fmul_rn( pr[1], a.g[1] ) );
+#pragma unroll
+            for( int i = 2; i <= S; i++ ) acc = __fmaf_rn( pr[i], a.g[i], acc );
+        }
+        V[r][cc] = acc;
+    }
+    __syncthreads();
+    const int lx = threadIdx.x & ( FXW - 1 ), x = x0 + lx;
+    if( x >= a.w ) return;
+#pragma unroll
+    for( int k = 0; k < FXH / 4; k++ ) {
+        const int r = ( threadIdx.x >> 6 ) + 4 * k, y = y0 + r;
+        if( y >= a.h ) break;
+        const float* v = &V[r][lx + S];
+        float out = __fmaf_rn( v[0], a.g[0], __fmul_rn( __fadd_rn( v[-1], v[1] ), a.g[1] ) );
+#pragma unroll
+        for( int i = 2; i <= S; i++ ) out = __fmaf_rn( __fadd_rn( v[-i], v[i] ), a.g[i], out );
+        if( FROM_TEX ) out = __fmul_rn( out, 255.0f );
+        a.dst[(size_t)y * a.pitch + x] = out;
+        if( a.ds_dst && !( x & 1 ) && !( y & 1 ) ) a.ds_dst[(size_t)( y >> 1 ) * a.ds_pitch + ( x >> 1 )] = out;
+    }
+}
+
+template<int S>
+static cudaError_t launch_pyramid_fixed( const PyrLayout& L, cudaTextureObject_t input_tex, float up_pow, const GaussTables& T,
+                                         cudaStream_t st, long long* launches )
+{
+    const int ds_level = L.n_lvl - 3;
+    for( int o = L.oct_begin; o < L.oct_end; o++ ) {
+        for( int l = ( o == 0 ? 0 : 1 ); l < L.n_lvl; l++ ) {
+            FixedArgs a;
+            a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
+            a.dst = L.base[o] + (size_t)l * L.lstride[o];
+            a.ds_dst = nullptr; a.ds_pitch = 0;
+            if( l == ds_level && o + 1 < L.alloc_end ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
+            a.tshift = 0.5f * up_pow;                               /* s_pyramid_fixed.cu:219 */
+            const Taps& t = ( o == 0 ) ? T.abs_o0[l] : T.abs_oN[l];
+            for( int i = 0; i < 8; i++ ) a.g[i] = t.g[i];
+            const dim3 grid( ( a.w + FXW - 1 ) / FXW, ( a.h + FXH - 1 ) / FXH );
+            cudaError_t e;
+            if( o == 0 ) { a.src = nullptr; a.tex = input_tex; e = launch_pdl( k_fixed_level<S, true>, grid, dim3( 256 ), 0, st, a ); }
+            else         { a.src = L.base[o]; a.tex = 0;       e = launch_pdl( k_fixed_level<S, false>, grid, dim3( 256 ), 0, st, a ); }
+            if( e != cudaSuccess ) return e;
+            if( launches ) ++*launches;
+        }
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode,
                             const GaussTables& T, const PyrStreams& S, long long* launches )
 {
     /* VLFeat_Relative_All ("vlfeat-direct"): every level of octave 0 is filtered straight from the
      * input image with the absolute tables (horiz_all + vert_all_abs0, s_pyramid_build.cu:545-548,
      * s_pyramid_build_ra.cu:93-129, s_pyramid_build_aa.cu:133-176); the other octaves are built as usual. */
+    if( gauss_mode == PSIFT_GAUSS_FIXED9 )  return launch_pyramid_fixed<4>( L, input_tex, up_pow, T, S.chain, launches );
+    if( gauss_mode == PSIFT_GAUSS_FIXED15 ) return launch_pyramid_fixed<7>( L, input_tex, up_pow, T, S.chain, launches );
     const bool direct_o0 = gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE_ALL;
     const int  ds_level = L.n_lvl - 3;      /* _levels - PREV_LEVEL, s_pyramid_build.cu:229 */
     const bool fork = S.side[0] != nullptr;

@@ -15,7 +15,7 @@ struct PyrStreams {
     cudaEvent_t  seeded[MAX_OCT];    /* level `levels` of octave o is complete */
     cudaEvent_t  side_done[2];
 };
-cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, int gauss_mode,
+cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode,
                             const GaussTables& T, const PyrStreams& S, long long* launches );
 /* k_extrema.cu */
 cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted,

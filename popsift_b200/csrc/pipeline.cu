@@ -336,7 +336,7 @@ static int run_frame( psift_ctx* c, Slot& s )
     float shift = 0.5f;                                              /* s_pyramid_build.cu:110-114 */
     if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT )
         shift = 0.5f * powf( 2.0f, c->cfg.upscale_factor );
-    CU( launch_pyramid( L, s.img_tex, shift, c->cfg.gauss_mode, c->gt, s.ps, &c->launches ) );
+    CU( launch_pyramid( L, s.img_tex, shift, powf( 2.0f, c->cfg.upscale_factor ), c->cfg.gauss_mode, c->gt, s.ps, &c->launches ) );
     CU( cudaEventRecord( s.ev[2], st ) );
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
@@ -413,9 +413,12 @@ int psift_device_count( void )
 static int check_config( const psift_config* cfg )
 {
     if( !cfg ) return fail( PSIFT_E_INVALID, "null config" );
+    const bool fixed = cfg->gauss_mode == PSIFT_GAUSS_FIXED9 || cfg->gauss_mode == PSIFT_GAUSS_FIXED15;
     if( cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_COMPUTE && cfg->gauss_mode != PSIFT_GAUSS_OPENCV_COMPUTE &&
-        cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE_ALL )
-        return fail( PSIFT_E_INVALID, "gauss mode %d not built yet (vlfeat, vlfeat-direct and opencv are)", cfg->gauss_mode );
+        cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE_ALL && !fixed )
+        return fail( PSIFT_E_INVALID, "gauss mode %d not built yet (vlfeat, vlfeat-direct, opencv, fixed9 and fixed15 are)", cfg->gauss_mode );
+    if( fixed && cfg->levels != 3 )           /* s_pyramid_fixed.cu:270-289: "Unsupported number of levels for making all octaves at once" */
+        return fail( PSIFT_E_INVALID, "the fixed9/fixed15 Gauss modes need levels = 3 (6 Gaussian levels), as in the reference" );
     if( cfg->desc_mode < 0 || cfg->desc_mode > PSIFT_DESC_NOTILE ) return fail( PSIFT_E_INVALID, "bad desc mode" );
     if( cfg->sift_mode < 0 || cfg->sift_mode > PSIFT_MODE_VLFEAT ) return fail( PSIFT_E_INVALID, "bad sift mode" );
     if( cfg->max_extrema < 1 ) return fail( PSIFT_E_INVALID, "max_extrema must be positive" );
@@ -533,6 +536,8 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
                           const Region& reg = Region() )
 {
     if( !c || !out || !src ) return fail( PSIFT_E_INVALID, "null argument" );
+    if( reg.kind != 0 && ( c->cfg.gauss_mode == PSIFT_GAUSS_FIXED9 || c->cfg.gauss_mode == PSIFT_GAUSS_FIXED15 ) )
+        return fail( PSIFT_E_INVALID, "banded extraction is not available for the fixed9/fixed15 Gauss modes" );
     if( reg.kind != 0 && c->cfg.filter_max_extrema > 0 ) return fail( PSIFT_E_INVALID, "the grid filter needs all keypoints of the image: not available for banded extraction" );
     *out = nullptr;
     if( w < 1 || h < 1 ) return fail( PSIFT_E_INVALID, "bad image size %dx%d", w, h );

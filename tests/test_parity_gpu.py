@@ -188,7 +188,9 @@ ORACLE_CASES = [(200, 150, 21, []), (97, 131, 22, []), (320, 240, 23, ["--mode",
                 (400, 300, 28, ["--filter-max-extrema", "120", "--filter-grid", "4", "--filter-sort", "down"]),
                 (400, 300, 29, ["--filter-max-extrema", "90", "--filter-grid", "3", "--filter-sort", "up"]),
                 (400, 300, 30, ["--filter-max-extrema", "100", "--filter-grid", "5", "--filter-sort", "random"]),
-                (256, 192, 31, ["--desc-mode", "iloop"]), (192, 256, 32, ["--gauss-mode", "vlfeat-direct"])]
+                (256, 192, 31, ["--desc-mode", "iloop"]), (192, 256, 32, ["--gauss-mode", "vlfeat-direct"]),
+                (211, 173, 33, ["--gauss-mode", "fixed9"]), (256, 200, 34, ["--gauss-mode", "fixed15"]),
+                (150, 220, 35, ["--gauss-mode", "fixed15", "--downsampling", "0", "--mode", "vlfeat"])]
 
 
 @pytest.mark.skipif(not os.path.exists(ORACLE), reason="oracle/cpu_sift not built")
