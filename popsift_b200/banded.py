@@ -37,6 +37,20 @@ class Merged:
         self.n_octaves, self.n_levels, self.w0, self.h0 = parts[0].n_octaves, parts[0].n_levels, parts[0].w0, parts[0].h0
 
 
+def digest(ex):
+    """Order-independent checksum of an Extraction / Merged: (sum of CRC32 over the feature records without their
+    descriptor indices, sum of CRC32 over the descriptor rows).  Sums over disjoint parts add up to the whole's."""
+    import zlib
+    f = ex.feat
+    rec = np.zeros(len(f), dtype=[("o", "<i4"), ("x", "<f4"), ("y", "<f4"), ("s", "<f4"), ("n", "<i4"), ("a", "<f4", (4,))])
+    rec["o"], rec["x"], rec["y"], rec["s"], rec["n"], rec["a"] = f["octave"], f["x"], f["y"], f["sigma"], f["num_ori"], f["ori"]
+    fb = rec.tobytes(); n = rec.dtype.itemsize
+    fs = sum(zlib.crc32(fb[i * n:(i + 1) * n]) for i in range(len(rec)))
+    db = np.ascontiguousarray(ex.desc, np.float32).tobytes()
+    ds = sum(zlib.crc32(db[i * 512:(i + 1) * 512]) for i in range(len(ex.desc)))
+    return fs, ds
+
+
 def _own_seed_rows(bounds, r, split, seed_h):
     """rows of octave split+1 that band r contributes to the gathered plane: a partition of [0, seed_h)"""
     lo = bounds[r] >> (split + 1)

@@ -17,10 +17,12 @@ with capi.Context(cfg, device=local) as ctx:
     torch.cuda.synchronize(); dist.barrier(); t0 = time.perf_counter()
     mine, split, bounds = banded.extract_banded_dist(ctx, img, cfg)
     torch.cuda.synchronize(); dist.barrier(); dt = time.perf_counter() - t0
-    counts = torch.tensor([mine.n_feat, mine.n_desc], device="cuda"); dist.all_reduce(counts)
+    fs, ds = banded.digest(mine)
+    counts = torch.tensor([mine.n_feat, mine.n_desc, fs, ds], device="cuda", dtype=torch.int64); dist.all_reduce(counts)
     if rank == 0:
         ctx.extract(img); t1 = time.perf_counter(); whole = ctx.extract(img); t2 = time.perf_counter()
         ok = (int(counts[0]), int(counts[1])) == (whole.n_feat, whole.n_desc)
+        same = (int(counts[2]), int(counts[3])) == banded.digest(whole)
         print({"w": W, "h": H, "ranks": world, "split_octave": split, "bounds": bounds, "banded_s": round(dt, 4), "whole_1gpu_s": round(t2 - t1, 4),
-               "features": int(counts[0]), "descriptors": int(counts[1]), "whole": (whole.n_feat, whole.n_desc), "counts_equal": ok})
+               "features": int(counts[0]), "descriptors": int(counts[1]), "whole": (whole.n_feat, whole.n_desc), "counts_equal": ok, "checksums_equal": same})
 dist.destroy_process_group()
