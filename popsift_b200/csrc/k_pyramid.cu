@@ -379,6 +379,282 @@ k_blur2( const __grid_constant__ BlurArgs a )
     }
 }
 
+/* ------------------------------------------------------------------------------------------
+ * v3, "marching" blur for the large planes.  The tile kernels above recompute (and re-read) 2H halo
+ * rows per 32-row tile - 1.3x (11 taps) to 1.8x (27 taps) of the horizontal pass - and pay two block
+ * barriers plus a window of 2H+8 shared-memory reads per 8 outputs in the vertical pass.  Here ONE WARP
+ * owns a strip of MW columns and walks down a segment of rows, RS rows per step:
+ *   1. the RS source rows of the step three ahead are requested (4-byte cp.async straight into the row-pair
+ *      interleaved layout of a ring of staging buffers: L2 latency hides behind three steps of arithmetic);
+ *   2. horizontal pass, 4 columns x 2 rows per lane out of a register window, result to shared memory;
+ *   3. vertical pass: every lane keeps the last 2H+RS horizontal results of ITS two columns in
+ *      registers (a sliding window), reads only the RS new ones, and emits RS output rows.
+ * So every source value is read from global memory once per strip (halo columns aside), every
+ * horizontal result is computed once and read from shared memory once, and there is no block barrier
+ * at all (__syncwarp only; the warps of a block drift apart and overlap their phases).  Vertical
+ * redundancy is 2H rows per SEGMENT (hundreds of rows), not per tile.  Same arithmetic, same order,
+ * same packed instructions as k_blur2: planes stay bit-identical.
+ * ------------------------------------------------------------------------------------------ */
+constexpr int MW     = 64;       /* strip width (columns per warp) */
+constexpr int MWARPS = 4;        /* warps per block; they do not cooperate */
+
+struct MarchArgs {
+    BlurArgs b;
+    int nstrip, nseg, seg_rows;  /* seg_rows: multiple of RS */
+};
+
+__device__ __forceinline__ void cp_async4( void* smem_dst, const void* gsrc )
+{
+    asm volatile( "cp.async.ca.shared.global [%0], [%1], 4;" :: "r"( (unsigned)__cvta_generic_to_shared( smem_dst ) ), "l"( gsrc ) : "memory" );
+}
+__device__ __forceinline__ void st_pred_v2( float* p, float2 v, bool ok )
+{
+    asm volatile( "{ .reg .pred q; setp.ne.b32 q, %0, 0; @q st.global.v2.f32 [%1], {%2, %3}; }" :: "r"( (int)ok ), "l"( p ), "f"( v.x ), "f"( v.y ) : "memory" );
+}
+__device__ __forceinline__ void st_pred( float* p, float v, bool ok )
+{
+    asm volatile( "{ .reg .pred q; setp.ne.b32 q, %0, 0; @q st.global.f32 [%1], %2; }" :: "r"( (int)ok ), "l"( p ), "f"( v ) : "memory" );
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile( "cp.async.commit_group;" ::: "memory" ); }
+template<int N> __device__ __forceinline__ void cp_async_wait() { asm volatile( "cp.async.wait_group %0;" :: "n"( N ) : "memory" ); }
+
+template<int H, int RS>
+struct MarchGeo {
+    static constexpr int HX  = ( H + 3 ) / 4 * 4;        /* x halo, padded to whole 16-byte words */
+    static constexpr int SW  = MW + 2 * HX;               /* staged columns */
+    static constexpr int NRP = RS / 2;                    /* row pairs per step */
+    static constexpr int M   = NRP;                       /* 2-column chunks are dealt round-robin into M arrays: lanes that are
+                                                             M chunks apart in the horizontal pass then read consecutive words */
+    static constexpr int LPR = 32 / NRP;                  /* lanes per row pair in the horizontal pass */
+    static constexpr int CPL = MW / LPR;                  /* columns per lane there (== RS) */
+    static constexpr int ASm = ( SW / 2 + M - 1 ) / M;
+    static constexpr int AS  = ASm + ( ( 8 / M - ASm % 8 ) + 8 ) % 8;   /* array stride in 16-byte words, == 8/M (mod 8): the M arrays
+                                                             then land on disjoint banks for the staging writes of a half warp */
+    static constexpr int RPB  = M * AS;                   /* 16-byte words per row pair */
+    static constexpr int SBUF = NRP * RPB;                /* ... per staging buffer */
+    static constexpr int PD   = RS >= 8 ? 2 : 3;          /* source rows are requested PD steps ahead ... */
+    static constexpr int NB   = PD + 1;                   /* ... into a ring of NB staging buffers */
+    static constexpr int NK   = ( SW + 15 ) / 16;         /* 16-column groups per staged row */
+    static constexpr int WARP_BYTES = NB * SBUF * 16 + RS * MW * 4;
+};
+
+template<int H, int RS, bool FROM_TEX>
+__global__ void __launch_bounds__( 32 * MWARPS, 2 )
+k_blur_march( const __grid_constant__ MarchArgs m )
+{
+    using G = MarchGeo<H, RS>;
+    const BlurArgs& a = m.b;
+    constexpr int HX = G::HX, SW = G::SW, NRP = G::NRP, M = G::M, LPR = G::LPR, CPL = G::CPL, AS = G::AS, RPB = G::RPB, SBUF = G::SBUF;
+    constexpr int PD = G::PD, NB = G::NB, NK = G::NK;
+    static_assert( CPL == 4 || CPL == 8, "horizontal pass: 4 or 8 columns per lane" );
+    constexpr int D = HX - H, W0 = D & ~1, E0 = D & 1, C = W0 / 2;
+    constexpr int WN = ( CPL + 2 * H + E0 + 1 ) & ~1;
+    extern __shared__ __align__( 16 ) float smem[];
+
+    pdl_enter();
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int wid  = blockIdx.x * MWARPS + wib;
+    if( wid >= m.nstrip * m.nseg ) return;
+    const int strip = wid % m.nstrip, seg = wid / m.nstrip;
+    const int x0 = strip * MW;
+    const int r0 = a.y_lo + seg * m.seg_rows;
+    const int r1 = min( r0 + m.seg_rows, a.y_hi );
+    const int nsteps = ( r1 - r0 + 2 * H + RS - 1 ) / RS;
+    const int w = a.w;
+    float4* S4 = reinterpret_cast<float4*>( reinterpret_cast<char*>( smem ) + wib * G::WARP_BYTES );   /* [NB][NRP][M][AS]: staged source rows */
+    float*  I  = reinterpret_cast<float*>( S4 + NB * SBUF );                                            /* [RS][MW]: horizontal results of this step */
+    const bool edge = x0 - HX < 0 || x0 + MW + HX > w;
+
+    /* staging: a half warp takes 16 consecutive columns of ONE row, the other half the same columns of the row below
+     * (the two rows of a pair sit in alternate 4-byte words, so the two halves never share a bank) */
+    const int hl = lane & 15, hp = lane >> 4;
+    const int sbase = ( ( ( hl >> 1 ) % M ) * AS + ( hl >> 1 ) / M ) * 4 + ( hl & 1 ) * 2 + hp;   /* floats, within a row pair; +32/M per group */
+    const int gx0 = x0 - HX + hl;
+    float rx[FROM_TEX ? NK : 1];
+    if( FROM_TEX ) {
+        #pragma unroll
+        for( int k = 0; k < NK; k++ ) rx[FROM_TEX ? k : 0] = __fdiv_rn( (float)( gx0 + 16 * k ) + a.shift, (float)w );   /* x unclamped: see k_blur_level */
+    }
+    /* request the RS source rows of step q into ring buffer q % NB.  Texture fetches return into registers:
+     * they are parked in tq[][] and stored one step later (store_tex), so that no warp waits on the texture unit */
+    float tq[FROM_TEX ? NRP : 1][FROM_TEX ? NK : 1];
+    auto request = [&]( int q ) {
+        float* sb = reinterpret_cast<float*>( S4 + ( q % NB ) * SBUF ) + sbase;
+        #pragma unroll
+        for( int rp = 0; rp < NRP; rp++ ) {
+            const int g = min( max( r0 - H + q * RS + 2 * rp + hp, a.y_lo ), a.y_hi - 1 );
+            if( FROM_TEX ) {
+                const float ry = __fdiv_rn( (float)g + a.shift, (float)a.h );
+                #pragma unroll
+                for( int k = 0; k < NK; k++ ) tq[FROM_TEX ? rp : 0][FROM_TEX ? k : 0] = tex2D<float>( a.tex, rx[FROM_TEX ? k : 0], ry );
+            } else {
+                const float* gr = a.src + (long long)g * a.pitch;
+                float* sr = sb + rp * RPB * 4;
+                if( !edge ) {
+                    #pragma unroll
+                    for( int k = 0; k < NK; k++ )
+                        if( 16 * k + 15 < SW || hl + 16 * k < SW ) cp_async4( sr + ( 32 / M ) * k, gr + gx0 + 16 * k );
+                } else {
+                    #pragma unroll
+                    for( int k = 0; k < NK; k++ )
+                        if( 16 * k + 15 < SW || hl + 16 * k < SW ) cp_async4( sr + ( 32 / M ) * k, gr + min( max( gx0 + 16 * k, 0 ), w - 1 ) );
+                }
+            }
+        }
+    };
+    auto store_tex = [&]( int q ) {
+        float* sb = reinterpret_cast<float*>( S4 + ( q % NB ) * SBUF ) + sbase;
+        #pragma unroll
+        for( int rp = 0; rp < NRP; rp++ ) {
+            #pragma unroll
+            for( int k = 0; k < NK; k++ )
+                if( 16 * k + 15 < SW || hl + 16 * k < SW ) sb[rp * RPB * 4 + ( 32 / M ) * k] = tq[FROM_TEX ? rp : 0][FROM_TEX ? k : 0];
+        }
+    };
+
+    float2 win[2 * H + RS];
+    #pragma unroll
+    for( int k = 0; k < 2 * H + RS; k++ ) win[k] = make_float2( 0.0f, 0.0f );
+    const int gxo = x0 + 2 * lane;                   /* this lane's output columns gxo, gxo+1 (w is even) */
+    /* horizontal pass: lane (p, g) filters columns CPL*g .. CPL*g+CPL-1 of row pair p */
+    const int hp_p = lane / LPR, hp_g = lane % LPR;
+    /* layout of I: row-major for CPL == 4; for CPL == 8 the two 4-column halves of every lane's 8 columns are kept in
+     * separate 32-float halves of the row, so that both the float4 stores and the float2 loads below are conflict-free */
+    float* const       i_st = I + 2 * hp_p * MW + 4 * hp_g;
+    const float* const i_ld = I + ( CPL == 8 ? ( ( lane & 3 ) >> 1 ) * 32 + ( lane >> 2 ) * 4 + ( lane & 1 ) * 2 : 2 * lane );
+
+    #pragma unroll
+    for( int q = 0; q < PD; q++ ) {
+        if( q < nsteps ) { request( q ); if( FROM_TEX ) store_tex( q ); }
+        cp_async_commit();
+    }
+    for( int s = 0; s < nsteps; s++ ) {
+        /* ---- 1. request the rows of step s + PD (into the buffer step s - 1 has finished with), wait for step s ---- */
+        if( FROM_TEX ) {
+            if( s > 0 && s - 1 + PD < nsteps ) store_tex( s - 1 + PD );     /* fetched during step s - 1 */
+            if( s + PD < nsteps ) request( s + PD );
+        } else {
+            if( s + PD < nsteps ) request( s + PD );
+            cp_async_commit();
+            cp_async_wait<PD>();
+        }
+        __syncwarp();
+
+        /* ---- 2. horizontal pass: CPL columns x 2 rows per lane ---- */
+        {
+            float2 hw[WN];
+            const float4* src = S4 + ( s % NB ) * SBUF + hp_p * RPB + hp_g;
+            #pragma unroll
+            for( int k = 0; k < WN / 2; k++ ) {
+                const float4 v = src[( ( C + k ) % M ) * AS + ( C + k ) / M];
+                hw[2 * k] = make_float2( v.x, v.y ); hw[2 * k + 1] = make_float2( v.z, v.w );
+            }
+            constexpr int C0 = E0 + H;
+            float2 o[CPL];
+            if( FROM_TEX ) {
+                #pragma unroll
+                for( int j = 0; j < CPL; j++ ) o[j] = make_float2( 0.0f, 0.0f );
+                #pragma unroll
+                for( int off = H; off > 0; off-- ) {
+                    #pragma unroll
+                    for( int j = 0; j < CPL; j++ ) o[j] = ffma2( fadd2( hw[C0 + j - off], hw[C0 + j + off] ), a.th.g[off], o[j] );
+                }
+                #pragma unroll
+                for( int j = 0; j < CPL; j++ ) o[j] = fmul2( ffma2( hw[C0 + j], a.th.g[0], o[j] ), 255.0f );
+            } else {
+                #pragma unroll
+                for( int j = 0; j < CPL; j++ ) o[j] = ffma2( hw[C0 + j], a.th.g[0], make_float2( 0.0f, 0.0f ) );
+                #pragma unroll
+                for( int off = H; off > 0; off-- ) {
+                    #pragma unroll
+                    for( int j = 0; j < CPL; j++ ) o[j] = ffma2( fadd2( hw[C0 + j - off], hw[C0 + j + off] ), a.th.g[off], o[j] );
+                }
+            }
+            #pragma unroll
+            for( int q = 0; q < CPL / 4; q++ ) {
+                *reinterpret_cast<float4*>( i_st + 32 * q )      = make_float4( o[4 * q].x, o[4 * q + 1].x, o[4 * q + 2].x, o[4 * q + 3].x );
+                *reinterpret_cast<float4*>( i_st + MW + 32 * q ) = make_float4( o[4 * q].y, o[4 * q + 1].y, o[4 * q + 2].y, o[4 * q + 3].y );
+            }
+        }
+        __syncwarp();
+
+        /* ---- 3. vertical pass: slide the register window down RS rows, emit RS output rows ---- */
+        #pragma unroll
+        for( int k = 0; k < 2 * H; k++ ) win[k] = win[k + RS];
+        #pragma unroll
+        for( int k = 0; k < RS; k++ ) win[2 * H + k] = *reinterpret_cast<const float2*>( i_ld + k * MW );
+        if( ( s + 1 ) * RS > 2 * H ) {
+            /* the RS accumulation chains are independent: written level by level so that they interleave, and the
+             * stores are predicated instructions, not branches (a branch per row makes the compiler sink each chain
+             * into its own block, where it runs as 2H+1 back-to-back dependent instructions) */
+            float2 acc[RS];
+            #pragma unroll
+            for( int j = 0; j < RS; j++ ) acc[j] = make_float2( 0.0f, 0.0f );
+            #pragma unroll
+            for( int off = H; off > 0; off-- ) {
+                #pragma unroll
+                for( int j = 0; j < RS; j++ ) acc[j] = ffma2( win[H + j - off], a.tv.g[off], acc[j] );
+                #pragma unroll
+                for( int j = 0; j < RS; j++ ) acc[j] = ffma2( win[H + j + off], a.tv.g[off], acc[j] );
+            }
+            #pragma unroll
+            for( int j = 0; j < RS; j++ ) acc[j] = ffma2( win[H + j], a.tv.g[0], acc[j] );
+            const int rowb = r0 - 2 * H + s * RS;        /* output row of j = 0; even, like r0 */
+            float* q  = a.dst + (long long)rowb * a.pitch + gxo;
+            float* qd = a.ds_dst + (long long)( rowb >> 1 ) * a.ds_pitch + ( gxo >> 1 );
+            const bool okx = gxo < w, okd = okx && a.ds_dst != nullptr;
+            #pragma unroll
+            for( int j = 0; j < RS; j++ ) {
+                const bool ok = (unsigned)( rowb + j - r0 ) < (unsigned)( r1 - r0 );
+                st_pred_v2( q + (long long)j * a.pitch, acc[j], ok && okx );
+                if( ( j & 1 ) == 0 ) st_pred( qd + (long long)( j >> 1 ) * a.ds_pitch, acc[j].x, ok && okd );
+            }
+        }
+    }
+}
+
+static int env_int( const char* name, int dflt )
+{
+    const char* e = getenv( name );
+    return e ? atoi( e ) : dflt;
+}
+static long march_min_px()   { static long v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH", 1 ) ? (long)env_int( "PSIFT_MARCH_MIN", 3000000 ) : 0x7fffffffffffL; return v; }
+static int  march_wps()      { static int v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH_WPS", 8 ); return v; }
+static bool march_tex()      { static int v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH_TEX", 1 ); return v != 0; }
+
+static int  march_rs()       { static int v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH_RS", 8 ); return v; }
+
+template<int H, int RS, bool FROM_TEX>
+static cudaError_t launch_march_rs( const BlurArgs& a, cudaStream_t st )
+{
+    using G = MarchGeo<H, RS>;
+    static int n_sm[16] = { 0 };
+    int dev = 0; cudaGetDevice( &dev );
+    int sms = dev < 16 ? n_sm[dev] : 0;
+    const size_t smem = (size_t)MWARPS * G::WARP_BYTES;
+    if( !sms ) {
+        cudaError_t e = cudaFuncSetAttribute( k_blur_march<H, RS, FROM_TEX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem );
+        if( e != cudaSuccess ) return e;
+        cudaDeviceGetAttribute( &sms, cudaDevAttrMultiProcessorCount, dev );
+        if( dev < 16 ) n_sm[dev] = sms;
+    }
+    MarchArgs m; m.b = a;
+    const int rows = a.y_hi - a.y_lo;
+    m.nstrip = ( a.w + MW - 1 ) / MW;
+    int nseg = std::max( 1, sms * march_wps() / m.nstrip );
+    m.seg_rows = std::max( 32, ( ( rows + nseg - 1 ) / nseg + RS - 1 ) / RS * RS );
+    m.nseg = ( rows + m.seg_rows - 1 ) / m.seg_rows;
+    const int blocks = ( m.nstrip * m.nseg + MWARPS - 1 ) / MWARPS;
+    return launch_pdl( k_blur_march<H, RS, FROM_TEX>, dim3( blocks ), dim3( 32 * MWARPS ), smem, st, m );
+}
+
+template<int H, bool FROM_TEX>
+static cudaError_t launch_march( const BlurArgs& a, cudaStream_t st )
+{
+    if( march_rs() == 4 ) return launch_march_rs<H, 4, FROM_TEX>( a, st );
+    return launch_march_rs<H, 8, FROM_TEX>( a, st );
+}
+
 static long blur_small_max()
 {
     static long v = -1;
@@ -406,6 +682,7 @@ static cudaError_t launch_v2t( const BlurArgs& a, cudaStream_t st )
 template<int H, bool FROM_TEX>
 static cudaError_t launch_v2( const BlurArgs& a, cudaStream_t st )
 {
+    if( (long)a.w * ( a.y_hi - a.y_lo ) >= march_min_px() && !( a.y_lo & 1 ) && !( a.w & 1 ) && ( !FROM_TEX || march_tex() ) ) return launch_march<H, FROM_TEX>( a, st );
     if( (long)a.w * ( a.y_hi - a.y_lo ) <= blur_small_max() ) return launch_v2t<H, FROM_TEX, TileSm>( a, st );
     return launch_v2t<H, FROM_TEX, TileMed>( a, st );
 }
