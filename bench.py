@@ -26,7 +26,9 @@ W, H = 1920, 1080
 BATCH = 25            # frames per step per GPU
 N_DISTINCT = 16       # distinct synthetic frames cycled through (seeds 1000..1015)
 IN_FLIGHT = 4
-PYRAMID_DRAM_BYTES = 229.1e6   # measured once per round with ncu (profiles/r01b_ncu_frame_summary.txt), per frame like algorithmic_bytes
+BLUR_DRAM_BYTES = 33.7e6       # dram read+write of one k_blur_march launch (3840x2160 level), ncu --set full: profiles/r01d_ncu_blur_march.txt
+PROFILE_SRC = "profiles/r01d_ncu_blur_march.txt"
+N_PYR_LAUNCHES = 46
 
 
 def pyramid_bytes(cfg_levels=3, up=1):
@@ -231,7 +233,30 @@ def main():
     a_pyr, sum_px, n_oct = pyramid_bytes()
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     peak = peaks.get("hbm_gbs", 6650.0)
-    achieved = a_pyr / (stage["pyramid"] * 1e-3) / 1e9
+    stage_achieved = a_pyr / (stage["pyramid"] * 1e-3) / 1e9
+
+    # dominant kernel, per launch: the blur launches of octave 0 (levels 1..5 = k_blur_march<H,8,0>; level 0 samples
+    # the input through the texture unit and is listed separately), each bracketed by CUDA events on the stream it is
+    # launched on (psift_debug_time_levels).  The stream is kept full (IN_FLIGHT frames) like the timed region above.
+    ctx.time_levels(True)
+    lv = []
+    q = []
+    for i in range(24):
+        q.append(sub_dev(dev_imgs[i % len(dev_imgs)]))
+        if len(q) >= IN_FLIGHT:
+            j = q.pop(0); ctx.wait(j, copy=False); ctx.free(j); lv.append(ctx.level_timing())
+    while q:
+        j = q.pop(0); ctx.wait(j, copy=False); ctx.free(j); lv.append(ctx.level_timing())
+    lv_alone = []
+    for i in range(8):
+        j = sub_dev(dev_imgs[i % len(dev_imgs)]); ctx.wait(j, copy=False); ctx.free(j); lv_alone.append(ctx.level_timing())
+    ctx.time_levels(False)
+    lv = np.median(np.array(lv[4:]), axis=0); lv_alone = np.median(np.array(lv_alone[2:]), axis=0)
+    w0, h0 = W * 2, H * 2
+    lvl_bytes = [W * H + 4 * w0 * h0] + [8 * w0 * h0] * 5          # level 0: u8 input + one fp32 plane; levels 1..5: read one plane, write one (A_pyr2 model)
+    lvl_bytes[3] += 4 * (w0 // 2) * (h0 // 2)                          # level 3 also writes the next octave's seed
+    dom_bytes = float(np.mean(lvl_bytes[1:])); dom_ms = float(np.mean(lv_alone[1:])); dom_ms_busy = float(np.mean(lv[1:]))
+    achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
 
     if rank == 0:
         line = {"metric": "images_per_sec_1080p", "value": world * n_frames / dt_dev, "unit": "images/s", "n_gpus": world,
@@ -248,9 +273,15 @@ def main():
                 "gpu_launches": int(launches),
                 "stage_ms": stage,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": PYRAMID_DRAM_BYTES, "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum over the 46 k_blur2 launches of one frame, ncu --set full, profiles/r01b_ncu_frame_summary.txt",
-                             "kernel": "k_blur2 (pyramid stage: %d launches per frame, three streams)" % (n_oct * 5 + 1),
-                             "algorithmic_bytes": a_pyr, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
+                             "traffic": BLUR_DRAM_BYTES, "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch of k_blur_march, ncu --set full (caches flushed before the launch), " + PROFILE_SRC,
+                             "kernel": "k_blur_march<H,8,0> (one Gaussian level of octave 0, 3840x2160: the 5 largest launches of a frame; H = 5,7,8,10,13 one-sided taps)",
+                             "algorithmic_bytes": dom_bytes, "launch_ms": dom_ms, "launch_ms_stream_full": dom_ms_busy,
+                             "per_level_ms": [float(x) for x in lv_alone], "per_level_ms_stream_full": [float(x) for x in lv],
+                             "per_level_bytes": lvl_bytes,
+                             "how": "algorithmic bytes per launch = 4 B read + 4 B written per pixel of the level (SURVEY 8d A_pyr2 model; +seed plane for level 3), over the mean duration of launches 1..5 (CUDA events on the launching stream, one frame at a time); per_level_ms[0] is the texture-sampling level-0 launch",
+                             "stage": {"achieved": stage_achieved, "frac": stage_achieved / peak, "algorithmic_bytes": a_pyr, "ms": stage["pyramid"],
+                                       "what": "whole pyramid stage (%d launches on three streams, deep octaves latency-bound): A_pyr = w*h + 4*L*sum(px), every level written once" % N_PYR_LAUNCHES},
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
                 "cpu_baseline": cpu_baseline() if not args.no_cpu else {"value": None, "unit": "images/s", "cores": 1, "kind": "port", "sample": "skipped (--no-cpu)"},
                 "clocks": cs.summary()}
         print(json.dumps(line))

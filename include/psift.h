@@ -166,6 +166,13 @@ int  psift_pyramid_geometry( const psift_config* cfg, int w, int h, int* w0, int
  * the context's stream): [0] upload, [1] pyramid, [2] extrema, [3] orientation, [4] descriptor+norm,
  * [5] download, [6] total.  For bench.py's roofline figures. */
 int  psift_last_timing( psift_ctx* ctx, float ms[8] );
+/* Per-launch timing of the dominant kernel: with time_levels on, every Gaussian-level launch of octave 0 (the six
+ * large blur launches of a frame) is bracketed by a CUDA-event pair on the stream it is launched on; after psift_wait,
+ * psift_last_level_timing returns their durations in milliseconds (ms[l] = level l, *n = levels).  The event records
+ * sit between programmatically dependent launches, so frames run a little slower while this is on: bench.py switches
+ * it on only for the frames it measures the roofline on. */
+int  psift_debug_time_levels( psift_ctx* ctx, int on );
+int  psift_last_level_timing( psift_ctx* ctx, float* ms, int cap, int* n );
 /* number of kernels this library launched since the context was created */
 long long psift_launch_count( psift_ctx* ctx );
 /* ---- one giant image over several GPUs (the reference has no such mode: it runs

@@ -51,7 +51,7 @@ EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "ps
            "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_wait",
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
-           "psift_launch_count", "psift_debug_mark", "psift_debug_mark_elapsed",
+           "psift_launch_count", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",
            "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32",
            "psift_wait_dev", "psift_dev_features_alloc", "psift_dev_features_free", "psift_dev_features_info", "psift_match",
            "psift_match_dev", "psift_dev_download", "psift_dev_upload"]
@@ -89,6 +89,8 @@ def lib():
         L.psift_band_seed_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int]
         L.psift_submit_seed_dev_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.psift_debug_mark.argtypes = [C.c_void_p, C.c_int]
+        L.psift_debug_time_levels.argtypes = [C.c_void_p, C.c_int]
+        L.psift_last_level_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_int)]
         L.psift_wait_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
         L.psift_dev_features_alloc.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.psift_dev_features_free.argtypes = [C.c_void_p]
@@ -263,6 +265,16 @@ class Context:
         ms = (C.c_float * 8)()
         _chk(lib().psift_last_timing(self._h, ms))
         return dict(zip(["upload", "pyramid", "extrema", "orientation", "descriptor", "download", "total"], [float(x) for x in ms[:7]]))
+
+    def time_levels(self, on):
+        """bracket every octave-0 blur launch with CUDA events on its own stream (psift_debug_time_levels)"""
+        _chk(lib().psift_debug_time_levels(self._h, 1 if on else 0))
+
+    def level_timing(self):
+        """durations (ms) of the octave-0 Gaussian-level launches of the last finished job, level 0 first"""
+        ms = (C.c_float * 16)(); n = C.c_int()
+        _chk(lib().psift_last_level_timing(self._h, ms, 16, C.byref(n)))
+        return [float(ms[i]) for i in range(n.value)]
 
     def mark(self, which):
         """device-side stopwatch (psift_debug_mark): 0 = start, 1 = stop"""

@@ -435,7 +435,12 @@ struct MarchGeo {
     static constexpr int PD   = RS >= 8 ? 2 : 3;          /* source rows are requested PD steps ahead ... */
     static constexpr int NB   = PD + 1;                   /* ... into a ring of NB staging buffers */
     static constexpr int NK   = ( SW + 15 ) / 16;         /* 16-column groups per staged row */
-    static constexpr int WARP_BYTES = NB * SBUF * 16 + RS * MW * 4;
+    /* horizontal results of a step: row-major for CPL == 4.  For CPL == 8 the two 4-column halves of every lane's 8
+     * columns live 48 floats apart in rows of 80 floats: the float4 stores of a quarter warp and the float2 loads of a
+     * half warp in the vertical pass then both touch every bank once */
+    static constexpr int IW   = CPL == 8 ? 80 : MW;       /* row stride of the horizontal results (floats) */
+    static constexpr int IH   = CPL == 8 ? 48 : 32;       /* offset of the second group of 4 columns */
+    static constexpr int WARP_BYTES = NB * SBUF * 16 + RS * IW * 4;
 };
 
 template<int H, int RS, bool FROM_TEX>
@@ -518,10 +523,9 @@ k_blur_march( const __grid_constant__ MarchArgs m )
     const int gxo = x0 + 2 * lane;                   /* this lane's output columns gxo, gxo+1 (w is even) */
     /* horizontal pass: lane (p, g) filters columns CPL*g .. CPL*g+CPL-1 of row pair p */
     const int hp_p = lane / LPR, hp_g = lane % LPR;
-    /* layout of I: row-major for CPL == 4; for CPL == 8 the two 4-column halves of every lane's 8 columns are kept in
-     * separate 32-float halves of the row, so that both the float4 stores and the float2 loads below are conflict-free */
-    float* const       i_st = I + 2 * hp_p * MW + 4 * hp_g;
-    const float* const i_ld = I + ( CPL == 8 ? ( ( lane & 3 ) >> 1 ) * 32 + ( lane >> 2 ) * 4 + ( lane & 1 ) * 2 : 2 * lane );
+    constexpr int IW = G::IW, IH = G::IH;
+    float* const       i_st = I + 2 * hp_p * IW + 4 * hp_g;
+    const float* const i_ld = I + ( CPL == 8 ? ( ( lane & 3 ) >> 1 ) * IH + ( lane >> 2 ) * 4 + ( lane & 1 ) * 2 : 2 * lane );
 
     #pragma unroll
     for( int q = 0; q < PD; q++ ) {
@@ -572,8 +576,8 @@ k_blur_march( const __grid_constant__ MarchArgs m )
             }
             #pragma unroll
             for( int q = 0; q < CPL / 4; q++ ) {
-                *reinterpret_cast<float4*>( i_st + 32 * q )      = make_float4( o[4 * q].x, o[4 * q + 1].x, o[4 * q + 2].x, o[4 * q + 3].x );
-                *reinterpret_cast<float4*>( i_st + MW + 32 * q ) = make_float4( o[4 * q].y, o[4 * q + 1].y, o[4 * q + 2].y, o[4 * q + 3].y );
+                *reinterpret_cast<float4*>( i_st + IH * q )      = make_float4( o[4 * q].x, o[4 * q + 1].x, o[4 * q + 2].x, o[4 * q + 3].x );
+                *reinterpret_cast<float4*>( i_st + IW + IH * q ) = make_float4( o[4 * q].y, o[4 * q + 1].y, o[4 * q + 2].y, o[4 * q + 3].y );
             }
         }
         __syncwarp();
@@ -582,7 +586,7 @@ k_blur_march( const __grid_constant__ MarchArgs m )
         #pragma unroll
         for( int k = 0; k < 2 * H; k++ ) win[k] = win[k + RS];
         #pragma unroll
-        for( int k = 0; k < RS; k++ ) win[2 * H + k] = *reinterpret_cast<const float2*>( i_ld + k * MW );
+        for( int k = 0; k < RS; k++ ) win[2 * H + k] = *reinterpret_cast<const float2*>( i_ld + k * IW );
         if( ( s + 1 ) * RS > 2 * H ) {
             /* the RS accumulation chains are independent: written level by level so that they interleave, and the
              * stores are predicated instructions, not branches (a branch per row makes the compiler sink each chain
@@ -754,6 +758,170 @@ static cudaError_t launch_blur( const BlurArgs& a, cudaStream_t st )
     }
 }
 
+/* ------------------------------------------------------------------------------------------
+ * Small octaves: several consecutive levels in ONE launch.  From octave 3 on (480x270 at 1080p) a level is a few
+ * microseconds of work, and a frame's pyramid time is the length of the dependency chain - level 1 -> 2 -> 3 of every
+ * octave, 5-6 us of launch + load + store latency each.  Here a block stages a 16x16 tile of the source level plus
+ * the SUM of the halos of the fused levels, and walks the levels in shared memory (horizontal pass into a second
+ * buffer, vertical pass back), storing its own tile of every level and the pick-every-second seed of the next octave.
+ * The halo cells are recomputed by the neighbouring blocks - a factor of 4-12 on planes that small is cheaper than
+ * one more launch in the chain.  One launch carries levels 1..levels of an octave on the chain stream, a second one
+ * the remaining two on a side stream.
+ *
+ * Clamp-to-edge is a property of READS in the reference (every level is read with clamped coordinates): the buffers
+ * keep the tile's frame of global coordinates and every tap clamps its global coordinate to the plane (rows: to the
+ * stored band) before indexing, so a cell outside the plane is never read and never needs a meaningful value.
+ * Arithmetic and tap order as in k_blur2: bit-identical planes.
+ * ------------------------------------------------------------------------------------------ */
+constexpr int FT       = 16;     /* tile (cells stored per block and level) */
+constexpr int FMAXR    = 24;     /* largest total one-sided halo of the fused levels */
+constexpr int FMAXL    = 3;      /* levels per launch */
+constexpr int FMAXTAP  = 16;
+
+struct MultiArgs {
+    const float* src;            /* the level below the first fused one */
+    float* dst[FMAXL];
+    float* ds_dst;               /* level 0 of the next octave, taken from fused level ds_idx (or nullptr) */
+    int    ds_pitch, ds_idx;
+    int    w, h, pitch, nl;
+    int    y_lo, y_hi;
+    int    hs[FMAXL];            /* one-sided tap count of each fused level */
+    float  g[FMAXL][FMAXTAP];
+};
+
+constexpr int FNT = 512;
+
+/* one level inside the block: horizontal pass A -> B on rows [m, RW-m) x columns [m+H, RW-m-H), then vertical pass
+ * B -> A on the square [m+H, RW-m-H); no clamping here - A is kept clamp-EXTENDED (see the kernel) */
+template<int H>
+__device__ __forceinline__ void multi_level( float* A, float* B, const float* g, int RW, int m, int R, int bx0, int by0,
+                                            int w, int y_hi, float* dst, int pitch, float* ds_dst, int ds_pitch )
+{
+    const int tid = threadIdx.x;
+    const int m1 = m + H;
+    const int hw_ = RW - 2 * m1, hh_ = RW - 2 * m;
+    for( int i = tid; i < hw_ * hh_; i += FNT ) {
+        const int r = m + i / hw_, c = m1 + i % hw_;
+        const float* p = A + r * RW + c;
+        float acc = __fmaf_rn( p[0], g[0], 0.0f );
+        #pragma unroll
+        for( int off = H; off > 0; off-- ) acc = __fmaf_rn( __fadd_rn( p[-off], p[off] ), g[off], acc );
+        B[r * RW + c] = acc;
+    }
+    __syncthreads();
+    for( int i = tid; i < hw_ * hw_; i += FNT ) {
+        const int r = m1 + i / hw_, c = m1 + i % hw_;
+        const float* p = B + r * RW + c;
+        float acc = 0.0f;
+        #pragma unroll
+        for( int off = H; off > 0; off-- ) {
+            acc = __fmaf_rn( p[-off * RW], g[off], acc );
+            acc = __fmaf_rn( p[ off * RW], g[off], acc );
+        }
+        acc = __fmaf_rn( p[0], g[0], acc );
+        A[r * RW + c] = acc;
+        const int gy = by0 + r, gx = bx0 + c;
+        if( r >= R && r < R + FT && c >= R && c < R + FT && gx < w && gy < y_hi ) {
+            dst[(size_t)gy * pitch + gx] = acc;
+            if( ds_dst && !( ( gx | gy ) & 1 ) ) ds_dst[(size_t)( gy >> 1 ) * ds_pitch + ( gx >> 1 )] = acc;
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__( FNT )
+k_blur_multi( const __grid_constant__ MultiArgs a )
+{
+    extern __shared__ __align__( 16 ) float smem[];
+    int R = 0;
+    for( int l = 0; l < a.nl; l++ ) R += a.hs[l];
+    const int RW = FT + 2 * R;                       /* edge of the square staged region */
+    float* A = smem;                                 /* current level, clamp-extended */
+    float* B = smem + RW * RW;                       /* its horizontal pass */
+    const int tid = threadIdx.x;
+    const int bx0 = blockIdx.x * FT - R;             /* global coordinates of buffer cell (0, 0) */
+    const int by0 = a.y_lo + blockIdx.y * FT - R;
+    const int w = a.w, y_lo = a.y_lo, y_hi = a.y_hi;
+    /* does the staged region stick out of the plane (the stored band)?  Then, after every level, the cells outside
+     * are overwritten with the value of the nearest cell inside: reading them is reading with clamped coordinates */
+    const bool border = bx0 < 0 || bx0 + RW > w || by0 < y_lo || by0 + RW > y_hi;
+    pdl_enter();
+
+    for( int i = tid; i < RW * RW; i += FNT ) {
+        const int r = i / RW, c = i - r * RW;
+        const int gx = min( max( bx0 + c, 0 ), w - 1 ), gy = min( max( by0 + r, y_lo ), y_hi - 1 );
+        A[i] = __ldg( a.src + (size_t)gy * a.pitch + gx );
+    }
+    __syncthreads();
+
+    int m = 0;                                       /* margin inside which the current level is valid */
+    for( int l = 0; l < a.nl; l++ ) {
+        float* ds = ( l == a.ds_idx ) ? a.ds_dst : nullptr;
+        switch( a.hs[l] ) {
+#define PSIFT_ML( HH ) case HH: multi_level<HH>( A, B, a.g[l], RW, m, R, bx0, by0, w, y_hi, a.dst[l], a.pitch, ds, a.ds_pitch ); break;
+        PSIFT_ML( 1 ) PSIFT_ML( 2 ) PSIFT_ML( 3 ) PSIFT_ML( 4 ) PSIFT_ML( 5 ) PSIFT_ML( 6 ) PSIFT_ML( 7 ) PSIFT_ML( 8 )
+        PSIFT_ML( 9 ) PSIFT_ML( 10 ) PSIFT_ML( 11 ) PSIFT_ML( 12 ) PSIFT_ML( 13 ) PSIFT_ML( 14 ) PSIFT_ML( 15 )
+#undef PSIFT_ML
+        default: break;
+        }
+        m += a.hs[l];
+        if( border && l + 1 < a.nl ) {
+            const int vw_ = RW - 2 * m;
+            for( int i = tid; i < vw_ * vw_; i += FNT ) {
+                const int r = m + i / vw_, c = m + i % vw_;
+                const int gx = bx0 + c, gy = by0 + r;
+                const int cx = min( max( gx, 0 ), w - 1 ), cy = min( max( gy, y_lo ), y_hi - 1 );
+                if( cx != gx || cy != gy ) A[r * RW + c] = A[( cy - by0 ) * RW + ( cx - bx0 )];
+            }
+            __syncthreads();
+        }
+    }
+}
+
+static long multi_max_px() { static long v = -1; if( v < 0 ) v = env_int( "PSIFT_MULTI", 0 ) ? (long)env_int( "PSIFT_MULTI_MAX", 300000 ) : 0; return v; }
+
+/* levels [l_first, l_last] of octave o in one launch; false if this configuration does not fit the kernel */
+static bool multi_fits( const GaussTables& T, int l_first, int l_last )
+{
+    if( l_last - l_first + 1 > FMAXL || l_last < l_first ) return false;
+    int R = 0;
+    for( int l = l_first; l <= l_last; l++ ) {
+        if( T.inc[l].span - 1 >= FMAXTAP || T.inc[l].span < 1 ) return false;
+        R += T.inc[l].span - 1;
+    }
+    return R <= FMAXR;
+}
+
+static cudaError_t launch_multi( const PyrLayout& L, const GaussTables& T, int o, int l_first, int l_last, int ds_level, cudaStream_t st )
+{
+    MultiArgs a;
+    a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
+    a.y_lo = L.row_lo[o]; a.y_hi = L.row_hi[o];
+    a.src = L.base[o] + (size_t)( l_first - 1 ) * L.lstride[o];
+    a.nl = l_last - l_first + 1;
+    a.ds_dst = nullptr; a.ds_pitch = 0; a.ds_idx = -1;
+    int R = 0;
+    for( int i = 0; i < FMAXL; i++ ) { a.dst[i] = nullptr; a.hs[i] = 0; }
+    for( int l = l_first; l <= l_last; l++ ) {
+        const int i = l - l_first;
+        a.dst[i] = L.base[o] + (size_t)l * L.lstride[o];
+        a.hs[i] = T.inc[l].span - 1;
+        R += a.hs[i];
+        for( int k = 0; k < FMAXTAP; k++ ) a.g[i][k] = T.inc[l].g[k];
+        if( l == ds_level && o + 1 < L.alloc_end ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; a.ds_idx = i; }
+    }
+    const size_t smem = sizeof(float) * 2 * ( FT + 2 * R ) * ( FT + 2 * R );
+    static bool attr_done[16] = { false };
+    int dev = 0; cudaGetDevice( &dev );
+    if( dev >= 16 || !attr_done[dev] ) {
+        cudaError_t e = cudaFuncSetAttribute( k_blur_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)( sizeof(float) * 2 * ( FT + 2 * FMAXR ) * ( FT + 2 * FMAXR ) ) );
+        if( e != cudaSuccess ) return e;
+        if( dev < 16 ) attr_done[dev] = true;
+    }
+    const dim3 grid( ( a.w + FT - 1 ) / FT, ( a.y_hi - a.y_lo + FT - 1 ) / FT );
+    return launch_pdl( k_blur_multi, grid, dim3( FNT ), smem, st, a );
+}
+
 /* Build every Gaussian level of every octave (reference Pyramid::build_pyramid,
  * s_pyramid_build.cu:460-596, default branch :549-577). */
 
@@ -868,6 +1036,21 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
     for( int o = L.oct_begin; o < L.oct_end; o++ ) {
         /* level 0 of octave 0 comes from the input image, of any other octave from the previous
          * octave's fused downscale (or, for the first octave of a seeded pass, from the caller) */
+        if( o > 0 && (long)L.w[o] * ( L.row_hi[o] - L.row_lo[o] ) <= multi_max_px() && ds_level >= 1 && ds_level < L.n_lvl - 1
+            && multi_fits( T, 1, ds_level ) && multi_fits( T, ds_level + 1, L.n_lvl - 1 ) ) {
+            /* small octave: levels 1..ds_level in one launch on the chain, the rest in one launch on a side stream */
+            if( ( e = launch_multi( L, T, o, 1, ds_level, ds_level, S.chain ) ) != cudaSuccess ) return e;
+            cudaStream_t st = S.chain;
+            if( fork ) {
+                st = S.side[o & 1];
+                if( ( e = cudaEventRecord( S.seeded[o], S.chain ) ) != cudaSuccess ) return e;
+                if( ( e = cudaStreamWaitEvent( st, S.seeded[o], 0 ) ) != cudaSuccess ) return e;
+                side_used[o & 1] = true;
+            }
+            if( ( e = launch_multi( L, T, o, ds_level + 1, L.n_lvl - 1, ds_level, st ) ) != cudaSuccess ) return e;
+            if( launches ) *launches += 2;
+            continue;
+        }
         for( int l = ( o == 0 ? 0 : 1 ); l < L.n_lvl; l++ ) {
             cudaStream_t st = S.chain;
             if( fork && l > ds_level ) {
@@ -885,6 +1068,8 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
             a.ds_dst = nullptr; a.ds_pitch = 0;
             if( l == ds_level && o + 1 < L.alloc_end ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
             a.shift = shift;
+            const bool timed = o == 0 && S.lvl_ev != nullptr;
+            if( timed && ( e = cudaEventRecord( S.lvl_ev[2 * l], st ) ) != cudaSuccess ) return e;
             if( o == 0 && direct_o0 ) {
                 a.src = nullptr; a.tex = input_tex;
                 a.th = T.abs_o0[l]; a.tv = T.abs_o0[l];
@@ -899,6 +1084,7 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
                 e = launch_blur<false>( a, st );
             }
             if( e != cudaSuccess ) return e;
+            if( timed && ( e = cudaEventRecord( S.lvl_ev[2 * l + 1], st ) ) != cudaSuccess ) return e;
             if( launches ) ++*launches;
         }
     }

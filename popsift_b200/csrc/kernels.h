@@ -14,6 +14,9 @@ struct PyrStreams {
     cudaStream_t side[2];
     cudaEvent_t  seeded[MAX_OCT];    /* level `levels` of octave o is complete */
     cudaEvent_t  side_done[2];
+    /* optional (psift_debug_time_levels): event pairs around every launch of octave 0, recorded on the stream the
+     * launch goes to; lvl_ev[2*l] before, lvl_ev[2*l+1] after level l.  nullptr: not timed */
+    cudaEvent_t* lvl_ev;
 };
 cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode,
                             const GaussTables& T, const PyrStreams& S, long long* launches );

@@ -41,6 +41,7 @@ struct Slot {
     cudaEvent_t  ev[N_EVENTS] = {};
     cudaEvent_t  ev_counters = nullptr;
     PyrStreams   ps = {};                                   /* chain = stream, two side streams, fork/join events */
+    cudaEvent_t  lvl_ev[2 * MAX_LVL] = {};                  /* psift_debug_time_levels */
     bool         busy = false;
 
     /* input */
@@ -86,6 +87,9 @@ struct psift_ctx {
     int next_slot = 0;
     long long launches = 0;
     float last_ms[8] = { 0 };
+    float last_lvl_ms[MAX_LVL] = { 0 };                     /* octave-0 launches of the last finished job, when timed */
+    int   last_lvl_n = 0;
+    bool  time_levels = false;
     int last_slot = -1;
     cudaStream_t mark_stream = nullptr;                     /* psift_debug_mark */
     cudaEvent_t  mark_ev[2] = { nullptr, nullptr };
@@ -123,6 +127,7 @@ static void free_slot( Slot& s )
     if( s.h_feat ) cudaFreeHost( s.h_feat );
     if( s.h_desc ) cudaFreeHost( s.h_desc );
     for( auto& e : s.ev ) if( e ) cudaEventDestroy( e );
+    for( auto& e : s.lvl_ev ) if( e ) cudaEventDestroy( e );
     if( s.ev_counters ) cudaEventDestroy( s.ev_counters );
     for( auto& e : s.ps.seeded ) if( e ) cudaEventDestroy( e );
     for( int k = 0; k < 2; k++ ) {
@@ -336,6 +341,11 @@ static int run_frame( psift_ctx* c, Slot& s )
     float shift = 0.5f;                                              /* s_pyramid_build.cu:110-114 */
     if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT )
         shift = 0.5f * powf( 2.0f, c->cfg.upscale_factor );
+    s.ps.lvl_ev = nullptr;
+    if( c->time_levels && L.oct_begin == 0 ) {
+        for( int k = 0; k < 2 * L.n_lvl; k++ ) if( !s.lvl_ev[k] ) CU( cudaEventCreate( &s.lvl_ev[k] ) );
+        s.ps.lvl_ev = s.lvl_ev;
+    }
     CU( launch_pyramid( L, s.img_tex, shift, powf( 2.0f, c->cfg.upscale_factor ), c->cfg.gauss_mode, c->gt, s.ps, &c->launches ) );
     CU( cudaEventRecord( s.ev[2], st ) );
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
@@ -703,6 +713,12 @@ int psift_wait( psift_job* j, psift_result* r )
         float ms = 0.f;
         for( int k = 0; k < 6; k++ ) { if( cudaEventElapsedTime( &ms, s.ev[k], s.ev[k + 1] ) == cudaSuccess ) c->last_ms[k] = ms; }
         if( cudaEventElapsedTime( &ms, s.ev[0], s.ev[6] ) == cudaSuccess ) c->last_ms[6] = ms;
+        c->last_lvl_n = 0;
+        if( s.ps.lvl_ev ) {
+            for( int l = 0; l < s.L.n_lvl; l++ )
+                c->last_lvl_ms[l] = cudaEventElapsedTime( &ms, s.lvl_ev[2 * l], s.lvl_ev[2 * l + 1] ) == cudaSuccess ? ms : -1.0f;
+            c->last_lvl_n = s.L.n_lvl;
+        }
         c->last_slot = j->slot;
     }
     memset( r, 0, sizeof *r );
@@ -766,6 +782,23 @@ int psift_last_timing( psift_ctx* c, float ms[8] )
     if( !c || !ms ) return fail( PSIFT_E_INVALID, "null argument" );
     std::lock_guard<std::mutex> lk( c->mu );
     memcpy( ms, c->last_ms, sizeof c->last_ms );
+    return PSIFT_OK;
+}
+
+int psift_debug_time_levels( psift_ctx* c, int on )
+{
+    if( !c ) return fail( PSIFT_E_INVALID, "null argument" );
+    std::lock_guard<std::mutex> lk( c->mu );
+    c->time_levels = on != 0;
+    return PSIFT_OK;
+}
+
+int psift_last_level_timing( psift_ctx* c, float* ms, int cap, int* n )
+{
+    if( !c || !ms || !n ) return fail( PSIFT_E_INVALID, "null argument" );
+    std::lock_guard<std::mutex> lk( c->mu );
+    *n = std::min( cap, c->last_lvl_n );
+    for( int l = 0; l < *n; l++ ) ms[l] = c->last_lvl_ms[l];
     return PSIFT_OK;
 }
 
