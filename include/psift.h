@@ -60,6 +60,9 @@ typedef struct psift_config {
     float initial_blur;         /* 0.5 */
     int   deterministic_order;  /* 1: features come back sorted (octave, level, y, x) -- an extension;
                                    the reference's order is whatever its atomics produced */
+    int   scaling_mode;         /* 0: every octave is seeded by the previous one (Config::ScaleDefault);
+                                   1: level 0 of EVERY octave is filtered straight from the input image
+                                   (Config::ScaleDirect, s_pyramid_build.cu:499-516) */
 } psift_config;
 
 /* One returned keypoint: field for field popsift::Feature (reference features.h:22-35), with

@@ -193,6 +193,12 @@ int main( int argc, char** argv )
         else if( a == "--filter-max-extrema" ) conf.setFilterMaxExtrema( atoi( next() ) );
         else if( a == "--filter-grid" )  conf.setFilterGridSize( atoi( next() ) );
         else if( a == "--filter-sort" )  conf.setFilterSorting( std::string( next() ) );
+        else if( a == "--scaling" ) {
+            std::string m = next();
+            if( m == "direct" ) conf.setScalingMode( Config::ScaleDirect );
+            else if( m == "default" ) conf.setScalingMode( Config::ScaleDefault );
+            else die( "bad --scaling" );
+        }
         else { fprintf( stderr, "ref_driver: unknown flag %s\n", a.c_str() ); return 2; }
     }
     if( !match_l.empty() ) return match_mode( match_l, match_r, out_prefix );

@@ -20,7 +20,7 @@ class Config(C.Structure):
                 ("sift_mode", C.c_int), ("desc_mode", C.c_int), ("norm_mode", C.c_int), ("norm_multi", C.c_int),
                 ("max_extrema", C.c_int), ("filter_max_extrema", C.c_int), ("filter_grid_size", C.c_int),
                 ("filter_sorting", C.c_int), ("assume_initial_blur", C.c_int), ("initial_blur", C.c_float),
-                ("deterministic_order", C.c_int)]
+                ("deterministic_order", C.c_int), ("scaling_mode", C.c_int)]
 
 
 FEATURE_DTYPE = np.dtype([("octave", "<i4"), ("x", "<f4"), ("y", "<f4"), ("sigma", "<f4"), ("num_ori", "<i4"),
@@ -125,6 +125,7 @@ def default_config(**kw):
         elif k == "norm_mode": cfg.norm_mode = NORM[v]
         elif k == "filter_sort": cfg.filter_sorting = FSORT[v]
         elif k == "downsampling": cfg.upscale_factor = -float(v)
+        elif k == "scaling": cfg.scaling_mode = {"default": 0, "direct": 1}[v]
         elif k == "initial_blur":
             cfg.initial_blur = float(v); cfg.assume_initial_blur = 0 if v == 0 else 1
         elif hasattr(cfg, k): setattr(cfg, k, v)
@@ -139,7 +140,7 @@ def config_from_flags(flags):
     for f in it:
         v = next(it)
         key = f.lstrip("-").replace("-", "_")
-        if key in ("mode", "gauss_mode", "desc_mode", "norm_mode", "filter_sort"): kw[key] = v
+        if key in ("mode", "gauss_mode", "desc_mode", "norm_mode", "filter_sort", "scaling"): kw[key] = v
         elif key == "downsampling": kw["downsampling"] = float(v)
         elif key in ("octaves", "levels", "norm_multi", "filter_max_extrema"): kw[key] = int(v)
         elif key == "filter_grid": kw["filter_grid_size"] = int(v)

@@ -134,6 +134,7 @@ void Config::toC( psift_config* c ) const
     c->max_extrema = _max_extrema; c->filter_max_extrema = _filter_max_extrema;
     c->filter_grid_size = _filter_grid_size; c->filter_sorting = (int)_grid_filter_mode;
     c->assume_initial_blur = _assume_initial_blur ? 1 : 0; c->initial_blur = _initial_blur;
+    c->scaling_mode = _scaling_mode == ScaleDirect ? 1 : 0;
 }
 
 } // namespace popsift

@@ -922,6 +922,129 @@ static cudaError_t launch_multi( const PyrLayout& L, const GaussTables& T, int o
     return launch_pdl( k_blur_multi, grid, dim3( FNT ), smem, st, a );
 }
 
+/* ------------------------------------------------------------------------------------------
+ * Gauss mode "relative" (VLFeat_Relative; reference s_pyramid_build_ai.cu:17-90 absoluteSourceInterpolated::horiz /
+ * vert, K5): two neighbouring taps a, b are folded into ONE bilinear texture fetch at the fractional position
+ * offset + (1 - u), u = a / (a + b), scaled by v = a + b (GaussTable::transformBlurTable, gauss_filter.cu:376-411).
+ * The blend is the texture unit's (9-bit weights), so the fetches stay on the texture unit here as well: linear
+ * textures over the pitch-linear planes, unnormalised coordinates + 0.5 (common/assist.h:66-81), clamp addressing.
+ * The horizontal pass goes to a scratch plane, the vertical pass reads that through its own texture.  Level 0 of
+ * octave 0 takes the ordinary horizontal pass over the input image (s_pyramid_build_ra.cu:17-55, one fetch per tap
+ * at read_x -+ offset / w exactly as there) and the interpolated vertical pass.  Accumulation as compiled in the
+ * reference build (SASS of oracle/_ref/obj/s_pyramid_build_ai.o): val = t(-off) + t(+off); out = fma(val, v, out);
+ * centre last.  Not a fast path: one thread per pixel.
+ * ------------------------------------------------------------------------------------------ */
+struct RelArgs {
+    cudaTextureObject_t src;
+    float* dst; float* ds_dst;
+    int   w, h, pitch, ds_pitch;
+    int   span, vertical;
+    float shift;
+    float f[TAP_ALIGN + 1];
+};
+
+__global__ void __launch_bounds__( 256 )
+k_rel_pass( const __grid_constant__ RelArgs a )
+{
+    pdl_enter();
+    const int x = blockIdx.x * 64 + ( threadIdx.x & 63 ), y = blockIdx.y * 4 + ( threadIdx.x >> 6 );
+    if( x >= a.w || y >= a.h ) return;
+    const float xf = (float)x, yf = (float)y;
+    float out = 0.0f;
+    for( int offset = 1; offset <= a.span; offset += 2 ) {
+        const float u   = a.f[offset];
+        const float off = __fadd_rn( (float)offset, __fsub_rn( 1.0f, u ) );
+        const float v   = a.f[offset + 1];
+        float t0, t1;
+        if( a.vertical ) {
+            t0 = tex2D<float>( a.src, __fadd_rn( xf, 0.5f ), __fadd_rn( __fsub_rn( yf, off ), 0.5f ) );
+            t1 = tex2D<float>( a.src, __fadd_rn( xf, 0.5f ), __fadd_rn( __fadd_rn( yf, off ), 0.5f ) );
+        } else {
+            t0 = tex2D<float>( a.src, __fadd_rn( __fsub_rn( xf, off ), 0.5f ), __fadd_rn( yf, 0.5f ) );
+            t1 = tex2D<float>( a.src, __fadd_rn( __fadd_rn( xf, off ), 0.5f ), __fadd_rn( yf, 0.5f ) );
+        }
+        out = __fmaf_rn( __fadd_rn( t0, t1 ), v, out );
+    }
+    out = __fmaf_rn( tex2D<float>( a.src, __fadd_rn( xf, 0.5f ), __fadd_rn( yf, 0.5f ) ), a.f[0], out );
+    a.dst[(size_t)y * a.pitch + x] = out;
+    if( a.ds_dst && !( ( x | y ) & 1 ) ) a.ds_dst[(size_t)( y >> 1 ) * a.ds_pitch + ( x >> 1 )] = out;
+}
+
+/* horizontal pass over the input image, one texture fetch per tap (s_pyramid_build_ra.cu:17-55) */
+__global__ void __launch_bounds__( 256 )
+k_rel_h_input( const __grid_constant__ RelArgs a )
+{
+    pdl_enter();
+    const int x = blockIdx.x * 64 + ( threadIdx.x & 63 ), y = blockIdx.y * 4 + ( threadIdx.x >> 6 );
+    if( x >= a.w || y >= a.h ) return;
+    const float read_x = __fdiv_rn( __fadd_rn( (float)x, a.shift ), (float)a.w );
+    const float read_y = __fdiv_rn( __fadd_rn( (float)y, a.shift ), (float)a.h );
+    float out = 0.0f;
+    for( int offset = a.span; offset > 0; offset-- ) {
+        const float offrel = __fdiv_rn( (float)offset, (float)a.w );
+        const float v1 = tex2D<float>( a.src, __fsub_rn( read_x, offrel ), read_y );
+        const float v2 = tex2D<float>( a.src, __fadd_rn( read_x, offrel ), read_y );
+        out = __fmaf_rn( __fadd_rn( v1, v2 ), a.f[offset], out );
+    }
+    out = __fmaf_rn( tex2D<float>( a.src, read_x, read_y ), a.f[0], out );
+    a.dst[(size_t)y * a.pitch + x] = __fmul_rn( out, 255.0f );
+}
+
+/* u / v table of one level (GaussTable::transformBlurTable, gauss_filter.cu:376-411) */
+static void rel_table( const Taps& t, RelArgs& a )
+{
+    int spn = t.span;
+    if( !( spn & 1 ) ) spn += 1;
+    a.span = spn;
+    for( int x = 0; x <= TAP_ALIGN; x++ ) a.f[x] = 0.0f;
+    for( int x = 1; x < spn && x + 1 < TAP_ALIGN; x += 2 ) {
+        const float ta = t.g[x], tb = t.g[x + 1];
+        a.f[x]     = ta / ( ta + tb );
+        a.f[x + 1] = ta + tb;
+    }
+    a.f[0] = t.g[0];
+}
+
+static cudaError_t launch_pyramid_relative( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, bool direct_scaling, const GaussTables& T,
+                                            const PyrStreams& S, long long* launches )
+{
+    if( !S.level_tex || !S.scratch_tex || !S.scratch ) return cudaErrorInvalidValue;
+    const int ds_level = L.n_lvl - 3;
+    cudaStream_t st = S.chain;
+    cudaError_t e;
+    for( int o = L.oct_begin; o < L.oct_end; o++ ) {
+        const dim3 grid( ( L.w[o] + 63 ) / 64, ( L.h[o] + 3 ) / 4 );
+        for( int l = ( o == 0 || direct_scaling ? 0 : 1 ); l < L.n_lvl; l++ ) {
+            RelArgs a;
+            a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
+            a.shift = o == 0 ? shift : 0.5f;                          /* s_pyramid_build.cu:110-114: the scaled shift is octave 0's */
+            /* horizontal pass -> scratch */
+            a.dst = S.scratch; a.ds_dst = nullptr; a.ds_pitch = 0; a.vertical = 0;
+            if( l == 0 ) {
+                a.src = input_tex;
+                a.span = T.dd[o].span;
+                for( int x = 0; x < TAP_ALIGN; x++ ) a.f[x] = T.dd[o].g[x];
+                a.f[TAP_ALIGN] = 0.0f;
+                e = launch_pdl( k_rel_h_input, grid, dim3( 256 ), 0, st, a );
+            } else {
+                a.src = S.level_tex[(size_t)o * L.n_lvl + ( l - 1 )];
+                rel_table( T.inc[l], a );
+                e = launch_pdl( k_rel_pass, grid, dim3( 256 ), 0, st, a );
+            }
+            if( e != cudaSuccess ) return e;
+            /* vertical pass scratch -> level l */
+            a.src = S.scratch_tex[o];
+            rel_table( T.inc[l], a );
+            a.vertical = 1;
+            a.dst = L.base[o] + (size_t)l * L.lstride[o];
+            if( l == ds_level && o + 1 < L.alloc_end && !direct_scaling ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
+            if( ( e = launch_pdl( k_rel_pass, grid, dim3( 256 ), 0, st, a ) ) != cudaSuccess ) return e;
+            if( launches ) *launches += 2;
+        }
+    }
+    return cudaSuccess;
+}
+
 /* Build every Gaussian level of every octave (reference Pyramid::build_pyramid,
  * s_pyramid_build.cu:460-596, default branch :549-577). */
 
@@ -1020,15 +1143,18 @@ static cudaError_t launch_pyramid_fixed( const PyrLayout& L, cudaTextureObject_t
     return cudaSuccess;
 }
 
-cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode,
+cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode, int scaling_mode,
                             const GaussTables& T, const PyrStreams& S, long long* launches )
 {
+    const bool direct_scaling = scaling_mode == 1;
     /* VLFeat_Relative_All ("vlfeat-direct"): every level of octave 0 is filtered straight from the
      * input image with the absolute tables (horiz_all + vert_all_abs0, s_pyramid_build.cu:545-548,
      * s_pyramid_build_ra.cu:93-129, s_pyramid_build_aa.cu:133-176); the other octaves are built as usual. */
+    if( gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE ) return launch_pyramid_relative( L, input_tex, shift, direct_scaling, T, S, launches );
     if( gauss_mode == PSIFT_GAUSS_FIXED9 )  return launch_pyramid_fixed<4>( L, input_tex, up_pow, T, S.chain, launches );
     if( gauss_mode == PSIFT_GAUSS_FIXED15 ) return launch_pyramid_fixed<7>( L, input_tex, up_pow, T, S.chain, launches );
-    const bool direct_o0 = gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE_ALL;
+    /* with ScaleDirect the reference never reaches its vlfeat-direct branch (s_pyramid_build.cu:499 comes first) */
+    const bool direct_o0 = gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE_ALL && !direct_scaling;
     const int  ds_level = L.n_lvl - 3;      /* _levels - PREV_LEVEL, s_pyramid_build.cu:229 */
     const bool fork = S.side[0] != nullptr;
     bool side_used[2] = { false, false };
@@ -1036,7 +1162,7 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
     for( int o = L.oct_begin; o < L.oct_end; o++ ) {
         /* level 0 of octave 0 comes from the input image, of any other octave from the previous
          * octave's fused downscale (or, for the first octave of a seeded pass, from the caller) */
-        if( o > 0 && (long)L.w[o] * ( L.row_hi[o] - L.row_lo[o] ) <= multi_max_px() && ds_level >= 1 && ds_level < L.n_lvl - 1
+        if( o > 0 && !direct_scaling && (long)L.w[o] * ( L.row_hi[o] - L.row_lo[o] ) <= multi_max_px() && ds_level >= 1 && ds_level < L.n_lvl - 1
             && multi_fits( T, 1, ds_level ) && multi_fits( T, ds_level + 1, L.n_lvl - 1 ) ) {
             /* small octave: levels 1..ds_level in one launch on the chain, the rest in one launch on a side stream */
             if( ( e = launch_multi( L, T, o, 1, ds_level, ds_level, S.chain ) ) != cudaSuccess ) return e;
@@ -1051,7 +1177,7 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
             if( launches ) *launches += 2;
             continue;
         }
-        for( int l = ( o == 0 ? 0 : 1 ); l < L.n_lvl; l++ ) {
+        for( int l = ( o == 0 || direct_scaling ? 0 : 1 ); l < L.n_lvl; l++ ) {
             cudaStream_t st = S.chain;
             if( fork && l > ds_level ) {
                 st = S.side[o & 1];
@@ -1066,8 +1192,8 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
             a.y_lo = L.row_lo[o]; a.y_hi = L.row_hi[o];
             a.dst = L.base[o] + (size_t)l * L.lstride[o];
             a.ds_dst = nullptr; a.ds_pitch = 0;
-            if( l == ds_level && o + 1 < L.alloc_end ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
-            a.shift = shift;
+            if( l == ds_level && o + 1 < L.alloc_end && !direct_scaling ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
+            a.shift = o == 0 ? shift : 0.5f;                          /* ScaleDirect: only octave 0 has the scaled shift, s_pyramid_build.cu:110-114 */
             const bool timed = o == 0 && S.lvl_ev != nullptr;
             if( timed && ( e = cudaEventRecord( S.lvl_ev[2 * l], st ) ) != cudaSuccess ) return e;
             if( o == 0 && direct_o0 ) {
@@ -1075,8 +1201,10 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
                 a.th = T.abs_o0[l]; a.tv = T.abs_o0[l];
                 e = launch_blur<true>( a, st );
             } else if( l == 0 ) {
+                /* ScaleDirect (s_pyramid_build.cu:499-516): horizontal pass with the octave's own table dd[o], vertical pass
+                 * with inc[0] (vert_from_interm( octave, 0, .. ) reads d_gauss.inc level 0 for every octave) */
                 a.src = nullptr; a.tex = input_tex;
-                a.th = T.dd[0]; a.tv = T.inc[0];
+                a.th = T.dd[o]; a.tv = T.inc[0];
                 e = launch_blur<true>( a, st );
             } else {
                 a.src = L.base[o] + (size_t)( l - 1 ) * L.lstride[o]; a.tex = 0;

@@ -17,8 +17,14 @@ struct PyrStreams {
     /* optional (psift_debug_time_levels): event pairs around every launch of octave 0, recorded on the stream the
      * launch goes to; lvl_ev[2*l] before, lvl_ev[2*l+1] after level l.  nullptr: not timed */
     cudaEvent_t* lvl_ev;
+    /* Gauss mode "relative" only (hardware-interpolated taps): bilinear textures over every Gaussian level
+     * (level_tex[o * n_lvl + l]) and over one scratch plane that takes the horizontal pass (scratch_tex[o]: the same
+     * memory seen with octave o's geometry) */
+    const cudaTextureObject_t* level_tex;
+    const cudaTextureObject_t* scratch_tex;
+    float* scratch;
 };
-cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode,
+cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode, int scaling_mode,
                             const GaussTables& T, const PyrStreams& S, long long* launches );
 /* k_extrema.cu */
 cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted,

@@ -57,6 +57,8 @@ struct Slot {
     int reg_kind = 0, reg_a = 0, reg_b = 0, reg_c = 0;     /* region the layout was built for (see Region) */
     std::vector<cudaTextureObject_t> lintex_h;
     cudaTextureObject_t* lintex_d = nullptr;
+    std::vector<cudaTextureObject_t> scratch_tex;          /* Gauss mode "relative": the scratch plane, one view per octave */
+    float* scratch = nullptr;
 
     /* keypoints */
     Cand* cand = nullptr; Cand* sorted = nullptr;
@@ -110,6 +112,8 @@ static void free_slot_pyramid( Slot& s )
 {
     for( auto t : s.lintex_h ) if( t ) cudaDestroyTextureObject( t );
     s.lintex_h.clear();
+    for( auto t : s.scratch_tex ) if( t ) cudaDestroyTextureObject( t );
+    s.scratch_tex.clear();
     if( s.lintex_d ) { cudaFree( s.lintex_d ); s.lintex_d = nullptr; }
     if( s.arena ) { cudaFree( s.arena ); s.arena = nullptr; s.arena_floats = 0; }
     s.in_w = s.in_h = 0;
@@ -211,6 +215,10 @@ static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h, const Region& reg
         ow = (int)ceilf( ow / 2.0f );
         oh = (int)ceilf( oh / 2.0f );
     }
+    const bool relative = c->cfg.gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE;
+    if( relative && reg.kind != 0 ) return fail( PSIFT_E_INVALID, "the relative Gauss mode is not available for banded extraction" );
+    const size_t scratch_off = total;
+    if( relative ) total += L.lstride[0];                                   /* horizontal-pass plane, octave-0 sized */
     if( total > s.arena_floats ) {
         free_slot_pyramid( s );
         CU( cudaMalloc( &s.arena, total * sizeof(float) ) );
@@ -218,14 +226,17 @@ static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h, const Region& reg
     } else {
         for( auto t : s.lintex_h ) if( t ) cudaDestroyTextureObject( t );
         s.lintex_h.clear();
+        for( auto t : s.scratch_tex ) if( t ) cudaDestroyTextureObject( t );
+        s.scratch_tex.clear();
     }
+    s.scratch = relative ? s.arena + scratch_off : nullptr;
     /* base[o] is where row 0 of the plane WOULD be: kernels address with global rows */
     for( int o = 0; o < n_oct; o++ )
         L.base[o] = reinterpret_cast<float*>( reinterpret_cast<uintptr_t>( s.arena + off[o] ) - sizeof(float) * (size_t)L.row_lo[o] * L.pitch[o] );
     s.L = L; s.in_w = w; s.in_h = h;
     s.reg_kind = reg.kind; s.reg_a = reg.y0; s.reg_b = reg.y1; s.reg_c = reg.split;
 
-    if( linear_needed( c->cfg.desc_mode ) ) {
+    if( linear_needed( c->cfg.desc_mode ) || relative ) {
         /* bilinear point-of-view of every Gaussian level (Octave::alloc_data_tex, sift_octave.cu:211-248) */
         if( reg.kind == 1 ) return fail( PSIFT_E_INVALID, "banded extraction supports the loop and grid descriptor modes only" );
         s.lintex_h.assign( (size_t)n_oct * n_lvl, 0 );
@@ -247,6 +258,24 @@ static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h, const Region& reg
         if( s.lintex_d ) cudaFree( s.lintex_d );
         CU( cudaMalloc( &s.lintex_d, s.lintex_h.size() * sizeof(cudaTextureObject_t) ) );
         CU( cudaMemcpy( s.lintex_d, s.lintex_h.data(), s.lintex_h.size() * sizeof(cudaTextureObject_t), cudaMemcpyHostToDevice ) );
+    }
+    if( relative ) {
+        /* the scratch plane seen with every octave's geometry (the reference's intermediate array, sift_octave.cu:250-330) */
+        s.scratch_tex.assign( (size_t)n_oct, 0 );
+        for( int o = 0; o < n_oct; o++ ) {
+            cudaResourceDesc rd; memset( &rd, 0, sizeof rd );
+            rd.resType = cudaResourceTypePitch2D;
+            rd.res.pitch2D.devPtr = s.scratch;
+            rd.res.pitch2D.desc = cudaCreateChannelDesc( 32, 0, 0, 0, cudaChannelFormatKindFloat );
+            rd.res.pitch2D.width = L.w[o]; rd.res.pitch2D.height = L.h[o];
+            rd.res.pitch2D.pitchInBytes = (size_t)L.pitch[o] * sizeof(float);
+            cudaTextureDesc td; memset( &td, 0, sizeof td );
+            td.normalizedCoords = 0;
+            td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+            td.readMode = cudaReadModeElementType;
+            td.filterMode = cudaFilterModeLinear;
+            CU( cudaCreateTextureObject( &s.scratch_tex[o], &rd, &td, nullptr ) );
+        }
     }
     return PSIFT_OK;
 }
@@ -341,12 +370,15 @@ static int run_frame( psift_ctx* c, Slot& s )
     float shift = 0.5f;                                              /* s_pyramid_build.cu:110-114 */
     if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT )
         shift = 0.5f * powf( 2.0f, c->cfg.upscale_factor );
+    s.ps.level_tex   = s.lintex_h.empty() ? nullptr : s.lintex_h.data();
+    s.ps.scratch_tex = s.scratch_tex.empty() ? nullptr : s.scratch_tex.data();
+    s.ps.scratch     = s.scratch;
     s.ps.lvl_ev = nullptr;
     if( c->time_levels && L.oct_begin == 0 ) {
         for( int k = 0; k < 2 * L.n_lvl; k++ ) if( !s.lvl_ev[k] ) CU( cudaEventCreate( &s.lvl_ev[k] ) );
         s.ps.lvl_ev = s.lvl_ev;
     }
-    CU( launch_pyramid( L, s.img_tex, shift, powf( 2.0f, c->cfg.upscale_factor ), c->cfg.gauss_mode, c->gt, s.ps, &c->launches ) );
+    CU( launch_pyramid( L, s.img_tex, shift, powf( 2.0f, c->cfg.upscale_factor ), c->cfg.gauss_mode, c->cfg.scaling_mode, c->gt, s.ps, &c->launches ) );
     CU( cudaEventRecord( s.ev[2], st ) );
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
@@ -411,6 +443,7 @@ void psift_config_default( psift_config* c )
     c->filter_sorting = PSIFT_FILTER_RANDOM;
     c->assume_initial_blur = 1; c->initial_blur = 0.5f;
     c->deterministic_order = 1;
+    c->scaling_mode = 0;
 }
 
 int psift_device_count( void )
@@ -425,8 +458,10 @@ static int check_config( const psift_config* cfg )
     if( !cfg ) return fail( PSIFT_E_INVALID, "null config" );
     const bool fixed = cfg->gauss_mode == PSIFT_GAUSS_FIXED9 || cfg->gauss_mode == PSIFT_GAUSS_FIXED15;
     if( cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_COMPUTE && cfg->gauss_mode != PSIFT_GAUSS_OPENCV_COMPUTE &&
-        cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE_ALL && !fixed )
-        return fail( PSIFT_E_INVALID, "gauss mode %d not built yet (vlfeat, vlfeat-direct, opencv, fixed9 and fixed15 are)", cfg->gauss_mode );
+        cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE_ALL && cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE && !fixed )
+        return fail( PSIFT_E_INVALID, "unknown gauss mode %d", cfg->gauss_mode );
+    if( cfg->scaling_mode != 0 && cfg->scaling_mode != 1 ) return fail( PSIFT_E_INVALID, "bad scaling mode" );
+    if( fixed && cfg->scaling_mode == 1 ) return fail( PSIFT_E_INVALID, "ScaleDirect is not built for the fixed9/fixed15 Gauss modes" );
     if( fixed && cfg->levels != 3 )           /* s_pyramid_fixed.cu:270-289: "Unsupported number of levels for making all octaves at once" */
         return fail( PSIFT_E_INVALID, "the fixed9/fixed15 Gauss modes need levels = 3 (6 Gaussian levels), as in the reference" );
     if( cfg->desc_mode < 0 || cfg->desc_mode > PSIFT_DESC_NOTILE ) return fail( PSIFT_E_INVALID, "bad desc mode" );

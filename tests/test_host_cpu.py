@@ -73,7 +73,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_sizes_match_header():
     assert capi.FEATURE_DTYPE.itemsize == 52 and capi.EXTREMUM_DTYPE.itemsize == 44
-    assert ctypes.sizeof(capi.Config) == 18 * 4
+    assert ctypes.sizeof(capi.Config) == 19 * 4
 
 
 def test_no_device_fails_loudly():

@@ -139,7 +139,12 @@ def _run_ref(tmp_path, img, flags, name):
 LIVE = [("c1_640x480_default", 640, 480, 1, []),
         ("c2_1080p_vlfeat_igrid", 1920, 1080, 2, ["--mode", "vlfeat", "--gauss-mode", "vlfeat", "--downsampling", "-1", "--desc-mode", "igrid"]),
         ("c4_1080p_default", 1920, 1080, 1000, []),
-        ("c3_4k_opencv_rootsift", 3840, 2160, 3, ["--mode", "opencv", "--gauss-mode", "opencv", "--norm-mode", "RootSift"])]
+        ("c3_4k_opencv_rootsift", 3840, 2160, 3, ["--mode", "opencv", "--gauss-mode", "opencv", "--norm-mode", "RootSift"]),
+        # the remaining Gauss / scaling variants at a size where every octave count and span occurs
+        ("n4_640x480_relative", 640, 480, 11, ["--gauss-mode", "relative"]),
+        ("n4_640x480_scaledirect", 640, 480, 12, ["--scaling", "direct"]),
+        ("n4_640x480_scaledirect_relative", 640, 480, 13, ["--scaling", "direct", "--gauss-mode", "relative"]),
+        ("n4_640x480_scaledirect_opencv", 640, 480, 14, ["--scaling", "direct", "--mode", "opencv", "--gauss-mode", "opencv"])]
 
 
 @pytest.mark.skipif(not os.path.exists(REF_DRIVER), reason="oracle/_ref/ref_driver not built")

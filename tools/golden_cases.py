@@ -54,6 +54,10 @@ CASES = {
     "g64_direct":       ("g64",    ["--gauss-mode", "vlfeat-direct"], True),
     "g256_direct":      ("g256",   ["--gauss-mode", "vlfeat-direct"], False),
     "g64_relative":     ("g64",    ["--gauss-mode", "relative"], True),
+    "g64_scaledirect":  ("g64",    ["--scaling", "direct"], True),
+    "g256_scaledirect": ("g256",   ["--scaling", "direct"], False),
+    "g64_scaledirect_rel": ("g64", ["--scaling", "direct", "--gauss-mode", "relative"], True),
+    "g256_relative":    ("g256",   ["--gauss-mode", "relative"], False),
     "g64_fixed9":       ("g64",    ["--gauss-mode", "fixed9"], True),
     "g64_fixed15":      ("g64",    ["--gauss-mode", "fixed15"], True),
 }
