@@ -42,6 +42,13 @@ struct Slot {
     cudaEvent_t  ev_counters = nullptr;
     PyrStreams   ps = {};                                   /* chain = stream, two side streams, fork/join events */
     cudaEvent_t  lvl_ev[2 * MAX_LVL] = {};                  /* psift_debug_time_levels */
+    /* the frame as a CUDA graph: captured from the very launches run_frame() makes, replayed for every later frame of
+     * the same shape (the ~60 launches, event forks and joins of a frame cost the submitting thread 0.26 ms as stream
+     * calls, 0.02 ms as one graph launch).  epoch counts every change of a pointer or size baked into the graph. */
+    cudaGraphExec_t graph = nullptr;
+    unsigned long long epoch = 1, graph_epoch = 0;
+    long long graph_launches = 0;
+    int  frames_direct = 0;
     bool         busy = false;
 
     /* input */
@@ -132,6 +139,7 @@ static void free_slot( Slot& s )
     if( s.h_desc ) cudaFreeHost( s.h_desc );
     for( auto& e : s.ev ) if( e ) cudaEventDestroy( e );
     for( auto& e : s.lvl_ev ) if( e ) cudaEventDestroy( e );
+    if( s.graph ) { cudaGraphExecDestroy( s.graph ); s.graph = nullptr; }
     if( s.ev_counters ) cudaEventDestroy( s.ev_counters );
     for( auto& e : s.ps.seeded ) if( e ) cudaEventDestroy( e );
     for( int k = 0; k < 2; k++ ) {
@@ -233,7 +241,7 @@ static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h, const Region& reg
     /* base[o] is where row 0 of the plane WOULD be: kernels address with global rows */
     for( int o = 0; o < n_oct; o++ )
         L.base[o] = reinterpret_cast<float*>( reinterpret_cast<uintptr_t>( s.arena + off[o] ) - sizeof(float) * (size_t)L.row_lo[o] * L.pitch[o] );
-    s.L = L; s.in_w = w; s.in_h = h;
+    s.L = L; s.in_w = w; s.in_h = h; s.epoch++;
     s.reg_kind = reg.kind; s.reg_a = reg.y0; s.reg_b = reg.y1; s.reg_c = reg.split;
 
     if( linear_needed( c->cfg.desc_mode ) || relative ) {
@@ -297,6 +305,7 @@ static int bind_input_texture( Slot& s, const void* dptr, size_t pitch, int w, i
     td.readMode = ( elem == 1 ) ? cudaReadModeNormalizedFloat : cudaReadModeElementType;
     td.filterMode = cudaFilterModeLinear;
     CU( cudaCreateTextureObject( &s.img_tex, &rd, &td, nullptr ) );
+    s.epoch++;
     s.tex_bound_ptr = dptr; s.tex_bound_pitch = pitch; s.img_w = w; s.img_h = h; s.img_elem = elem;
     return PSIFT_OK;
 }
@@ -308,7 +317,7 @@ static int alloc_keypoint_buffers( Slot& s, int ext_cap, int desc_cap )
 {
     cudaFree( s.sorted ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.filt );
     s.sorted = nullptr; s.ext = nullptr; s.feat = nullptr; s.desc_map = nullptr; s.desc = nullptr; s.filt = nullptr;
-    s.ext_cap = ext_cap; s.desc_cap = desc_cap;
+    s.ext_cap = ext_cap; s.desc_cap = desc_cap; s.epoch++;
     CU( cudaMalloc( &s.sorted, sizeof(Cand) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.ext,    sizeof(psift_extremum) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.feat,   sizeof(psift_feature) * (size_t)ext_cap ) );
@@ -360,12 +369,21 @@ static int ensure_host_results( Slot& s, int n_ext, int n_desc )
     return PSIFT_OK;
 }
 
-/* queue one frame on the slot's stream; the input texture is already bound */
-static int run_frame( psift_ctx* c, Slot& s )
+static bool graphs_enabled()
+{
+    static int v = -1;
+    if( v < 0 ) { const char* e = getenv( "PSIFT_GRAPH" ); v = e ? atoi( e ) : 1; }
+    return v != 0;
+}
+
+/* the launches of one frame, onto the slot's stream (directly, or into a stream capture) */
+static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing )
 {
     cudaStream_t st = s.stream;
     const PyrLayout& L = s.L;
-    CU( cudaEventRecord( s.ev[1], st ) );
+    /* stage stamps: inside a graph they must be external event-record nodes to be readable afterwards */
+    auto stamp = [&]( cudaEvent_t e ) { return capturing ? cudaEventRecordWithFlags( e, st, cudaEventRecordExternal ) : cudaEventRecord( e, st ); };
+    CU( stamp( s.ev[1] ) );
     CU( cudaMemsetAsync( s.ct, 0, sizeof(Counters), st ) );           /* reset_extrema_mgmt, sift_pyramid.cu:363-370 */
     float shift = 0.5f;                                              /* s_pyramid_build.cu:110-114 */
     if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT )
@@ -374,21 +392,57 @@ static int run_frame( psift_ctx* c, Slot& s )
     s.ps.scratch_tex = s.scratch_tex.empty() ? nullptr : s.scratch_tex.data();
     s.ps.scratch     = s.scratch;
     s.ps.lvl_ev = nullptr;
-    if( c->time_levels && L.oct_begin == 0 ) {
+    if( !capturing && c->time_levels && L.oct_begin == 0 ) {
         for( int k = 0; k < 2 * L.n_lvl; k++ ) if( !s.lvl_ev[k] ) CU( cudaEventCreate( &s.lvl_ev[k] ) );
         s.ps.lvl_ev = s.lvl_ev;
     }
     CU( launch_pyramid( L, s.img_tex, shift, powf( 2.0f, c->cfg.upscale_factor ), c->cfg.gauss_mode, c->cfg.scaling_mode, c->gt, s.ps, &c->launches ) );
-    CU( cudaEventRecord( s.ev[2], st ) );
+    CU( stamp( s.ev[2] ) );
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
-    CU( cudaEventRecord( s.ev[3], st ) );
+    CU( stamp( s.ev[3] ) );
     CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, 148 * 10, st, &c->launches ) );
-    CU( cudaEventRecord( s.ev[4], st ) );
+    CU( stamp( s.ev[4] ) );
     CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.lintex_d, c->d_dt, s.desc, s.feat, 148 * 4, st, &c->launches ) );
-    CU( cudaEventRecord( s.ev[5], st ) );
+    CU( stamp( s.ev[5] ) );
     CU( cudaMemcpyAsync( s.h_ct, s.ct, sizeof(Counters), cudaMemcpyDeviceToHost, st ) );
-    CU( cudaEventRecord( s.ev_counters, st ) );
+    return PSIFT_OK;
+}
+
+/* queue one frame on the slot's stream; the input texture is already bound.  Whole-image frames run as a CUDA graph
+ * from their second use on (the first one runs as plain launches: it also sets the kernels' attributes, which must
+ * not happen inside a capture); banded / seeded passes and per-level timing keep plain launches. */
+static int run_frame( psift_ctx* c, Slot& s )
+{
+    const bool want_graph = graphs_enabled() && s.reg_kind == 0 && !c->time_levels && s.frames_direct > 0;
+    if( want_graph && ( !s.graph || s.graph_epoch != s.epoch ) ) {
+        if( s.graph ) { cudaGraphExecDestroy( s.graph ); s.graph = nullptr; }
+        const long long l0 = c->launches;
+        cudaGraph_t g = nullptr;
+        CU( cudaStreamBeginCapture( s.stream, cudaStreamCaptureModeRelaxed ) );
+        const int rc = enqueue_frame( c, s, true );
+        const cudaError_t ee = cudaStreamEndCapture( s.stream, &g );
+        s.graph_launches = c->launches - l0;
+        c->launches = l0;
+        if( rc != PSIFT_OK || ee != cudaSuccess || !g ) {
+            if( g ) cudaGraphDestroy( g );
+            cudaGetLastError();
+            return rc != PSIFT_OK ? rc : fail( PSIFT_E_CUDA, "frame capture: %s", cudaGetErrorString( ee ) );
+        }
+        const cudaError_t ei = cudaGraphInstantiate( &s.graph, g, 0 );
+        cudaGraphDestroy( g );
+        if( ei != cudaSuccess ) { s.graph = nullptr; return fail( PSIFT_E_CUDA, "frame graph: %s", cudaGetErrorString( ei ) ); }
+        s.graph_epoch = s.epoch;
+    }
+    if( want_graph ) {
+        CU( cudaGraphLaunch( s.graph, s.stream ) );
+        c->launches += s.graph_launches;
+    } else {
+        const int rc = enqueue_frame( c, s, false );
+        if( rc ) return rc;
+        s.frames_direct++;
+    }
+    CU( cudaEventRecord( s.ev_counters, s.stream ) );
     return PSIFT_OK;
 }
 
@@ -539,7 +593,12 @@ int psift_configure( psift_ctx* c, const psift_config* cfg_in )
     CU( cudaMemcpy( c->d_dt, &c->dt, sizeof(DescTables), cudaMemcpyHostToDevice ) );
     if( realloc_slots ) {
         for( auto& s : c->slots ) free_slot( s );
-        c->slots.assign( 4, Slot() );
+        /* frames in flight per context: each slot owns a pyramid arena (265 MB at 1080p), keypoint buffers and streams.
+         * Four keep the GPU busy when the inputs are already on the device; with host inputs every frame also spends
+         * about 0.3 ms outside the GPU (pinned copy, upload, the waiter's wake-up, result download), which more slots hide */
+        int n_slots = 6;
+        if( const char* e = getenv( "PSIFT_SLOTS" ) ) n_slots = std::min( 16, std::max( 1, atoi( e ) ) );
+        c->slots.assign( (size_t)n_slots, Slot() );
         for( auto& s : c->slots ) { rc = init_slot( c, s ); if( rc ) return rc; }
     } else {
         for( auto& s : c->slots ) free_slot_pyramid( s );      /* geometry may change with the config */
@@ -612,24 +671,40 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
     } else if( on_device ) {
         if( pitch % 32 || ( (uintptr_t)src % 512 ) )
             return fail( PSIFT_E_INVALID, "device image needs a 512-byte aligned base and a pitch that is a multiple of 32" );
-        rc = bind_input_texture( s, src, pitch, w, h, elem );
+        if( graphs_enabled() && reg.kind == 0 ) {
+            /* the frame graph has the input texture baked in: keep the texture on the slot's own image buffer and
+             * bring the caller's image there (2 MB device-to-device at 1080p, about a microsecond) */
+            const size_t row = (size_t)w * elem;
+            if( !s.d_img || s.img_cap_w < row || s.img_cap_h < (size_t)h ) {
+                if( s.img_tex ) { cudaDestroyTextureObject( s.img_tex ); s.img_tex = 0; }
+                if( s.d_img ) cudaFree( s.d_img );
+                s.img_cap_w = std::max( s.img_cap_w, row ); s.img_cap_h = std::max( s.img_cap_h, (size_t)h );
+                CU( cudaMallocPitch( &s.d_img, &s.img_pitch, s.img_cap_w, s.img_cap_h ) );
+            }
+            CU( cudaMemcpy2DAsync( s.d_img, s.img_pitch, src, pitch, row, h, cudaMemcpyDeviceToDevice, s.stream ) );
+            rc = bind_input_texture( s, s.d_img, s.img_pitch, w, h, elem );
+        } else
+            rc = bind_input_texture( s, src, pitch, w, h, elem );
         if( rc ) return rc;
     } else {
         /* private pinned copy (SiftJob::SiftJob, popsift.cpp:238-253; Image::load, s_image.cu:71-79) */
-        const size_t row = (size_t)w * elem, need = row * h;
-        if( need > s.h_img_cap ) {
-            if( s.h_img ) cudaFreeHost( s.h_img );
-            CU( cudaMallocHost( &s.h_img, need ) );
-            s.h_img_cap = need;
-        }
-        for( int y = 0; y < h; y++ ) memcpy( (char*)s.h_img + y * row, (const char*)src + y * pitch, row );
+        const size_t row = (size_t)w * elem;
         if( !s.d_img || s.img_cap_w < row || s.img_cap_h < (size_t)h ) {
             if( s.img_tex ) { cudaDestroyTextureObject( s.img_tex ); s.img_tex = 0; }
             if( s.d_img ) cudaFree( s.d_img );
             s.img_cap_w = std::max( s.img_cap_w, row ); s.img_cap_h = std::max( s.img_cap_h, (size_t)h );
             CU( cudaMallocPitch( &s.d_img, &s.img_pitch, s.img_cap_w, s.img_cap_h ) );
         }
-        CU( cudaMemcpy2DAsync( s.d_img, s.img_pitch, s.h_img, row, row, h, cudaMemcpyHostToDevice, s.stream ) );
+        /* the pinned copy has the DEVICE pitch, so that the upload is one linear transfer and not a row-by-row 2-D copy */
+        const size_t need = s.img_pitch * h;
+        if( need > s.h_img_cap ) {
+            if( s.h_img ) cudaFreeHost( s.h_img );
+            CU( cudaMallocHost( &s.h_img, need ) );
+            s.h_img_cap = need;
+        }
+        if( pitch == s.img_pitch ) memcpy( s.h_img, src, pitch * ( h - 1 ) + row );
+        else for( int y = 0; y < h; y++ ) memcpy( (char*)s.h_img + y * s.img_pitch, (const char*)src + y * pitch, row );
+        CU( cudaMemcpyAsync( s.d_img, s.h_img, need, cudaMemcpyHostToDevice, s.stream ) );
         rc = bind_input_texture( s, s.d_img, s.img_pitch, w, h, elem );
         if( rc ) return rc;
     }
