@@ -220,7 +220,9 @@ def main():
     with ClockSampler(local) as cs:
         dt_dev, nf, nd, wall_dev = timed(sub_dev, dev_imgs)
     launches = (ctx.launch_count() - l0) * args.steps // (args.steps + args.warmup)
+    b0 = ctx.d2h_bytes()
     dt_e2e, nf2, nd2, wall_e2e = timed(sub_host, imgs)
+    d2h_per_step = (ctx.d2h_bytes() - b0) // (args.steps + args.warmup)
     n_frames = args.steps * BATCH
 
     # kernel-stage times (CUDA events on the frame's stream), one frame at a time, warm
@@ -269,7 +271,8 @@ def main():
                            "timing": "CUDA events joining all of the context's streams around the K steps (max over ranks); wall clock of the same region in wall_ms_per_step; stage times from CUDA events on the frame's stream",
                            "features_per_frame": nf / n_frames, "descriptors_per_frame": nd / n_frames},
                 "e2e": {"value": world * n_frames / dt_e2e, "unit": "images/s", "wall_value": world * n_frames / wall_e2e, "h2d_bytes_per_step": W * H * BATCH,
-                        "d2h_bytes_per_step": int((nf2 * (52 + 44) + nd2 * 512) / args.steps)},
+                        "d2h_bytes_per_step": int(d2h_per_step),
+                        "d2h_note": "result bytes actually queued for download (each frame copies a prefix sized from earlier frames, +25 %%, so that no host round trip sits between the kernels and the download); the frames hold %d bytes of results per step" % int((nf2 * (52 + 44) + nd2 * 512) / args.steps)},
                 "gpu_launches": int(launches),
                 "stage_ms": stage,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

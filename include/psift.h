@@ -178,6 +178,8 @@ int  psift_debug_time_levels( psift_ctx* ctx, int on );
 int  psift_last_level_timing( psift_ctx* ctx, float* ms, int cap, int* n );
 /* number of kernels this library launched since the context was created */
 long long psift_launch_count( psift_ctx* ctx );
+/* result bytes (counters, keypoint records, descriptors) queued for download to the host since the context was created */
+long long psift_d2h_bytes( psift_ctx* ctx );
 /* ---- one giant image over several GPUs (the reference has no such mode: it runs
  * config 5 un-tiled on one GPU, sift_pyramid.cu:108-165) -------------------------------------------
  * The image is cut into row bands, one per context (GPU).  Every context gets the WHOLE u8 image (it is

@@ -384,9 +384,9 @@ k_blur2( const __grid_constant__ BlurArgs a )
  * rows per 32-row tile - 1.3x (11 taps) to 1.8x (27 taps) of the horizontal pass - and pay two block
  * barriers plus a window of 2H+8 shared-memory reads per 8 outputs in the vertical pass.  Here ONE WARP
  * owns a strip of MW columns and walks down a segment of rows, RS rows per step:
- *   1. the RS source rows of the step three ahead are requested (4-byte cp.async straight into the row-pair
- *      interleaved layout of a ring of staging buffers: L2 latency hides behind three steps of arithmetic);
- *   2. horizontal pass, 4 columns x 2 rows per lane out of a register window, result to shared memory;
+ *   1. the RS source rows of the step two ahead are requested (4-byte cp.async straight into the row-pair
+ *      interleaved layout of a ring of staging buffers: L2 latency hides behind two steps of arithmetic);
+ *   2. horizontal pass, RS columns x 2 rows per lane out of a register window, result to shared memory;
  *   3. vertical pass: every lane keeps the last 2H+RS horizontal results of ITS two columns in
  *      registers (a sliding window), reads only the RS new ones, and emits RS output rows.
  * So every source value is read from global memory once per strip (halo columns aside), every
@@ -394,6 +394,11 @@ k_blur2( const __grid_constant__ BlurArgs a )
  * at all (__syncwarp only; the warps of a block drift apart and overlap their phases).  Vertical
  * redundancy is 2H rows per SEGMENT (hundreds of rows), not per tile.  Same arithmetic, same order,
  * same packed instructions as k_blur2: planes stay bit-identical.
+ *
+ * Measured (B200, a 3840x2160 level, ncu with flushed caches): 19.8 ... 32.6 us for 11 ... 27 taps against 23.0 ...
+ * 43.1 us for k_blur2.  What bounds it (profiles/r01d_ncu_blur_march.txt): a step of the 11-tap level is 176 packed
+ * FFMA2/FADD2 (two issue cycles each) plus about 250 other instructions for 512 pixels, so the issue slots, not HBM
+ * (66 MB in 20 us = 3.3 TB/s), set the time; more warps per SM do not help (8 and 16 were measured equal).
  * ------------------------------------------------------------------------------------------ */
 constexpr int MW     = 64;       /* strip width (columns per warp) */
 constexpr int MWARPS = 4;        /* warps per block; they do not cooperate */
@@ -626,7 +631,6 @@ static long march_min_px()   { static long v = -1; if( v < 0 ) v = env_int( "PSI
 static int  march_wps()      { static int v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH_WPS", 8 ); return v; }
 static bool march_tex()      { static int v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH_TEX", 1 ); return v != 0; }
 
-static int  march_rs()       { static int v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH_RS", 8 ); return v; }
 
 template<int H, int RS, bool FROM_TEX>
 static cudaError_t launch_march_rs( const BlurArgs& a, cudaStream_t st )
@@ -655,7 +659,8 @@ static cudaError_t launch_march_rs( const BlurArgs& a, cudaStream_t st )
 template<int H, bool FROM_TEX>
 static cudaError_t launch_march( const BlurArgs& a, cudaStream_t st )
 {
-    if( march_rs() == 4 ) return launch_march_rs<H, 4, FROM_TEX>( a, st );
+    /* 8 rows per step: 8 columns x 2 rows per lane in the horizontal pass (4 rows / 4 columns was measured too: the
+     * same time at twice the instructions per pixel for staging, barriers and addressing) */
     return launch_march_rs<H, 8, FROM_TEX>( a, st );
 }
 
@@ -756,170 +761,6 @@ static cudaError_t launch_blur( const BlurArgs& a, cudaStream_t st )
     case 7: return launch_hq<7, FROM_TEX>( a, st );
     default: return launch_hq<8, FROM_TEX>( a, st );
     }
-}
-
-/* ------------------------------------------------------------------------------------------
- * Small octaves: several consecutive levels in ONE launch.  From octave 3 on (480x270 at 1080p) a level is a few
- * microseconds of work, and a frame's pyramid time is the length of the dependency chain - level 1 -> 2 -> 3 of every
- * octave, 5-6 us of launch + load + store latency each.  Here a block stages a 16x16 tile of the source level plus
- * the SUM of the halos of the fused levels, and walks the levels in shared memory (horizontal pass into a second
- * buffer, vertical pass back), storing its own tile of every level and the pick-every-second seed of the next octave.
- * The halo cells are recomputed by the neighbouring blocks - a factor of 4-12 on planes that small is cheaper than
- * one more launch in the chain.  One launch carries levels 1..levels of an octave on the chain stream, a second one
- * the remaining two on a side stream.
- *
- * Clamp-to-edge is a property of READS in the reference (every level is read with clamped coordinates): the buffers
- * keep the tile's frame of global coordinates and every tap clamps its global coordinate to the plane (rows: to the
- * stored band) before indexing, so a cell outside the plane is never read and never needs a meaningful value.
- * Arithmetic and tap order as in k_blur2: bit-identical planes.
- * ------------------------------------------------------------------------------------------ */
-constexpr int FT       = 16;     /* tile (cells stored per block and level) */
-constexpr int FMAXR    = 24;     /* largest total one-sided halo of the fused levels */
-constexpr int FMAXL    = 3;      /* levels per launch */
-constexpr int FMAXTAP  = 16;
-
-struct MultiArgs {
-    const float* src;            /* the level below the first fused one */
-    float* dst[FMAXL];
-    float* ds_dst;               /* level 0 of the next octave, taken from fused level ds_idx (or nullptr) */
-    int    ds_pitch, ds_idx;
-    int    w, h, pitch, nl;
-    int    y_lo, y_hi;
-    int    hs[FMAXL];            /* one-sided tap count of each fused level */
-    float  g[FMAXL][FMAXTAP];
-};
-
-constexpr int FNT = 512;
-
-/* one level inside the block: horizontal pass A -> B on rows [m, RW-m) x columns [m+H, RW-m-H), then vertical pass
- * B -> A on the square [m+H, RW-m-H); no clamping here - A is kept clamp-EXTENDED (see the kernel) */
-template<int H>
-__device__ __forceinline__ void multi_level( float* A, float* B, const float* g, int RW, int m, int R, int bx0, int by0,
-                                            int w, int y_hi, float* dst, int pitch, float* ds_dst, int ds_pitch )
-{
-    const int tid = threadIdx.x;
-    const int m1 = m + H;
-    const int hw_ = RW - 2 * m1, hh_ = RW - 2 * m;
-    for( int i = tid; i < hw_ * hh_; i += FNT ) {
-        const int r = m + i / hw_, c = m1 + i % hw_;
-        const float* p = A + r * RW + c;
-        float acc = __fmaf_rn( p[0], g[0], 0.0f );
-        #pragma unroll
-        for( int off = H; off > 0; off-- ) acc = __fmaf_rn( __fadd_rn( p[-off], p[off] ), g[off], acc );
-        B[r * RW + c] = acc;
-    }
-    __syncthreads();
-    for( int i = tid; i < hw_ * hw_; i += FNT ) {
-        const int r = m1 + i / hw_, c = m1 + i % hw_;
-        const float* p = B + r * RW + c;
-        float acc = 0.0f;
-        #pragma unroll
-        for( int off = H; off > 0; off-- ) {
-            acc = __fmaf_rn( p[-off * RW], g[off], acc );
-            acc = __fmaf_rn( p[ off * RW], g[off], acc );
-        }
-        acc = __fmaf_rn( p[0], g[0], acc );
-        A[r * RW + c] = acc;
-        const int gy = by0 + r, gx = bx0 + c;
-        if( r >= R && r < R + FT && c >= R && c < R + FT && gx < w && gy < y_hi ) {
-            dst[(size_t)gy * pitch + gx] = acc;
-            if( ds_dst && !( ( gx | gy ) & 1 ) ) ds_dst[(size_t)( gy >> 1 ) * ds_pitch + ( gx >> 1 )] = acc;
-        }
-    }
-    __syncthreads();
-}
-
-__global__ void __launch_bounds__( FNT )
-k_blur_multi( const __grid_constant__ MultiArgs a )
-{
-    extern __shared__ __align__( 16 ) float smem[];
-    int R = 0;
-    for( int l = 0; l < a.nl; l++ ) R += a.hs[l];
-    const int RW = FT + 2 * R;                       /* edge of the square staged region */
-    float* A = smem;                                 /* current level, clamp-extended */
-    float* B = smem + RW * RW;                       /* its horizontal pass */
-    const int tid = threadIdx.x;
-    const int bx0 = blockIdx.x * FT - R;             /* global coordinates of buffer cell (0, 0) */
-    const int by0 = a.y_lo + blockIdx.y * FT - R;
-    const int w = a.w, y_lo = a.y_lo, y_hi = a.y_hi;
-    /* does the staged region stick out of the plane (the stored band)?  Then, after every level, the cells outside
-     * are overwritten with the value of the nearest cell inside: reading them is reading with clamped coordinates */
-    const bool border = bx0 < 0 || bx0 + RW > w || by0 < y_lo || by0 + RW > y_hi;
-    pdl_enter();
-
-    for( int i = tid; i < RW * RW; i += FNT ) {
-        const int r = i / RW, c = i - r * RW;
-        const int gx = min( max( bx0 + c, 0 ), w - 1 ), gy = min( max( by0 + r, y_lo ), y_hi - 1 );
-        A[i] = __ldg( a.src + (size_t)gy * a.pitch + gx );
-    }
-    __syncthreads();
-
-    int m = 0;                                       /* margin inside which the current level is valid */
-    for( int l = 0; l < a.nl; l++ ) {
-        float* ds = ( l == a.ds_idx ) ? a.ds_dst : nullptr;
-        switch( a.hs[l] ) {
-#define PSIFT_ML( HH ) case HH: multi_level<HH>( A, B, a.g[l], RW, m, R, bx0, by0, w, y_hi, a.dst[l], a.pitch, ds, a.ds_pitch ); break;
-        PSIFT_ML( 1 ) PSIFT_ML( 2 ) PSIFT_ML( 3 ) PSIFT_ML( 4 ) PSIFT_ML( 5 ) PSIFT_ML( 6 ) PSIFT_ML( 7 ) PSIFT_ML( 8 )
-        PSIFT_ML( 9 ) PSIFT_ML( 10 ) PSIFT_ML( 11 ) PSIFT_ML( 12 ) PSIFT_ML( 13 ) PSIFT_ML( 14 ) PSIFT_ML( 15 )
-#undef PSIFT_ML
-        default: break;
-        }
-        m += a.hs[l];
-        if( border && l + 1 < a.nl ) {
-            const int vw_ = RW - 2 * m;
-            for( int i = tid; i < vw_ * vw_; i += FNT ) {
-                const int r = m + i / vw_, c = m + i % vw_;
-                const int gx = bx0 + c, gy = by0 + r;
-                const int cx = min( max( gx, 0 ), w - 1 ), cy = min( max( gy, y_lo ), y_hi - 1 );
-                if( cx != gx || cy != gy ) A[r * RW + c] = A[( cy - by0 ) * RW + ( cx - bx0 )];
-            }
-            __syncthreads();
-        }
-    }
-}
-
-static long multi_max_px() { static long v = -1; if( v < 0 ) v = env_int( "PSIFT_MULTI", 0 ) ? (long)env_int( "PSIFT_MULTI_MAX", 300000 ) : 0; return v; }
-
-/* levels [l_first, l_last] of octave o in one launch; false if this configuration does not fit the kernel */
-static bool multi_fits( const GaussTables& T, int l_first, int l_last )
-{
-    if( l_last - l_first + 1 > FMAXL || l_last < l_first ) return false;
-    int R = 0;
-    for( int l = l_first; l <= l_last; l++ ) {
-        if( T.inc[l].span - 1 >= FMAXTAP || T.inc[l].span < 1 ) return false;
-        R += T.inc[l].span - 1;
-    }
-    return R <= FMAXR;
-}
-
-static cudaError_t launch_multi( const PyrLayout& L, const GaussTables& T, int o, int l_first, int l_last, int ds_level, cudaStream_t st )
-{
-    MultiArgs a;
-    a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
-    a.y_lo = L.row_lo[o]; a.y_hi = L.row_hi[o];
-    a.src = L.base[o] + (size_t)( l_first - 1 ) * L.lstride[o];
-    a.nl = l_last - l_first + 1;
-    a.ds_dst = nullptr; a.ds_pitch = 0; a.ds_idx = -1;
-    int R = 0;
-    for( int i = 0; i < FMAXL; i++ ) { a.dst[i] = nullptr; a.hs[i] = 0; }
-    for( int l = l_first; l <= l_last; l++ ) {
-        const int i = l - l_first;
-        a.dst[i] = L.base[o] + (size_t)l * L.lstride[o];
-        a.hs[i] = T.inc[l].span - 1;
-        R += a.hs[i];
-        for( int k = 0; k < FMAXTAP; k++ ) a.g[i][k] = T.inc[l].g[k];
-        if( l == ds_level && o + 1 < L.alloc_end ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; a.ds_idx = i; }
-    }
-    const size_t smem = sizeof(float) * 2 * ( FT + 2 * R ) * ( FT + 2 * R );
-    static bool attr_done[16] = { false };
-    int dev = 0; cudaGetDevice( &dev );
-    if( dev >= 16 || !attr_done[dev] ) {
-        cudaError_t e = cudaFuncSetAttribute( k_blur_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)( sizeof(float) * 2 * ( FT + 2 * FMAXR ) * ( FT + 2 * FMAXR ) ) );
-        if( e != cudaSuccess ) return e;
-        if( dev < 16 ) attr_done[dev] = true;
-    }
-    const dim3 grid( ( a.w + FT - 1 ) / FT, ( a.y_hi - a.y_lo + FT - 1 ) / FT );
-    return launch_pdl( k_blur_multi, grid, dim3( FNT ), smem, st, a );
 }
 
 /* ------------------------------------------------------------------------------------------
@@ -1162,21 +1003,6 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
     for( int o = L.oct_begin; o < L.oct_end; o++ ) {
         /* level 0 of octave 0 comes from the input image, of any other octave from the previous
          * octave's fused downscale (or, for the first octave of a seeded pass, from the caller) */
-        if( o > 0 && !direct_scaling && (long)L.w[o] * ( L.row_hi[o] - L.row_lo[o] ) <= multi_max_px() && ds_level >= 1 && ds_level < L.n_lvl - 1
-            && multi_fits( T, 1, ds_level ) && multi_fits( T, ds_level + 1, L.n_lvl - 1 ) ) {
-            /* small octave: levels 1..ds_level in one launch on the chain, the rest in one launch on a side stream */
-            if( ( e = launch_multi( L, T, o, 1, ds_level, ds_level, S.chain ) ) != cudaSuccess ) return e;
-            cudaStream_t st = S.chain;
-            if( fork ) {
-                st = S.side[o & 1];
-                if( ( e = cudaEventRecord( S.seeded[o], S.chain ) ) != cudaSuccess ) return e;
-                if( ( e = cudaStreamWaitEvent( st, S.seeded[o], 0 ) ) != cudaSuccess ) return e;
-                side_used[o & 1] = true;
-            }
-            if( ( e = launch_multi( L, T, o, ds_level + 1, L.n_lvl - 1, ds_level, st ) ) != cudaSuccess ) return e;
-            if( launches ) *launches += 2;
-            continue;
-        }
         for( int l = ( o == 0 || direct_scaling ? 0 : 1 ); l < L.n_lvl; l++ ) {
             cudaStream_t st = S.chain;
             if( fork && l > ds_level ) {

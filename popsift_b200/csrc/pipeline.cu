@@ -49,6 +49,10 @@ struct Slot {
     unsigned long long epoch = 1, graph_epoch = 0;
     long long graph_launches = 0;
     int  frames_direct = 0;
+    /* results are downloaded by the frame itself, without a round trip through the waiting thread: the first pre_ext
+     * keypoints and pre_desc descriptors (sized from the frames seen so far, +25 %) are copied right after the counters;
+     * psift_wait fetches the rest only when a frame has more.  run_pre_*: what the frame in flight was queued with. */
+    int  pre_ext = 0, pre_desc = 0, run_pre_ext = 0, run_pre_desc = 0;
     bool         busy = false;
 
     /* input */
@@ -96,6 +100,7 @@ struct psift_ctx {
     int next_slot = 0;
     long long launches = 0;
     float last_ms[8] = { 0 };
+    long long d2h_bytes = 0;                                /* result bytes queued for download so far */
     float last_lvl_ms[MAX_LVL] = { 0 };                     /* octave-0 launches of the last finished job, when timed */
     int   last_lvl_n = 0;
     bool  time_levels = false;
@@ -358,13 +363,13 @@ static int ensure_host_results( Slot& s, int n_ext, int n_desc )
         const int cap = std::max( 4096, n_ext + n_ext / 2 );
         CU( cudaMallocHost( &s.h_ext, sizeof(psift_extremum) * (size_t)cap ) );
         CU( cudaMallocHost( &s.h_feat, sizeof(psift_feature) * (size_t)cap ) );
-        s.h_ext_cap = cap;
+        s.h_ext_cap = cap; s.epoch++;
     }
     if( n_desc > s.h_desc_cap ) {
         if( s.h_desc ) cudaFreeHost( s.h_desc );
         const int cap = std::max( 8192, n_desc + n_desc / 2 );
         CU( cudaMallocHost( &s.h_desc, sizeof(float) * 128 * (size_t)cap ) );
-        s.h_desc_cap = cap;
+        s.h_desc_cap = cap; s.epoch++;
     }
     return PSIFT_OK;
 }
@@ -406,6 +411,12 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing )
     CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.lintex_d, c->d_dt, s.desc, s.feat, 148 * 4, st, &c->launches ) );
     CU( stamp( s.ev[5] ) );
     CU( cudaMemcpyAsync( s.h_ct, s.ct, sizeof(Counters), cudaMemcpyDeviceToHost, st ) );
+    if( s.pre_ext > 0 ) {
+        CU( cudaMemcpyAsync( s.h_feat, s.feat, sizeof(psift_feature)  * (size_t)s.pre_ext, cudaMemcpyDeviceToHost, st ) );
+        CU( cudaMemcpyAsync( s.h_ext,  s.ext,  sizeof(psift_extremum) * (size_t)s.pre_ext, cudaMemcpyDeviceToHost, st ) );
+    }
+    if( s.pre_desc > 0 )
+        CU( cudaMemcpyAsync( s.h_desc, s.desc, sizeof(float) * 128 * (size_t)s.pre_desc, cudaMemcpyDeviceToHost, st ) );
     return PSIFT_OK;
 }
 
@@ -414,6 +425,10 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing )
  * not happen inside a capture); banded / seeded passes and per-level timing keep plain launches. */
 static int run_frame( psift_ctx* c, Slot& s )
 {
+    s.pre_ext = std::min( s.pre_ext, s.ext_cap ); s.pre_desc = std::min( s.pre_desc, s.desc_cap );
+    if( s.pre_ext > 0 || s.pre_desc > 0 ) { const int rc = ensure_host_results( s, s.pre_ext, s.pre_desc ); if( rc ) return rc; }
+    s.run_pre_ext = s.pre_ext; s.run_pre_desc = s.pre_desc;
+    c->d2h_bytes += (long long)s.pre_ext * ( sizeof(psift_feature) + sizeof(psift_extremum) ) + (long long)s.pre_desc * 512 + sizeof(Counters);
     const bool want_graph = graphs_enabled() && s.reg_kind == 0 && !c->time_levels && s.frames_direct > 0;
     if( want_graph && ( !s.graph || s.graph_epoch != s.epoch ) ) {
         if( s.graph ) { cudaGraphExecDestroy( s.graph ); s.graph = nullptr; }
@@ -808,17 +823,28 @@ int psift_wait( psift_job* j, psift_result* r )
         int rc0 = settle_frame( c, s );
         if( rc0 ) return rc0;
         const int n_ext = s.h_ct->ext_total, n_desc = s.h_ct->ori_total;
-        int rc = ensure_host_results( s, n_ext, n_desc );
-        if( rc ) return rc;
-        if( n_ext > 0 ) {
-            CU( cudaMemcpyAsync( s.h_feat, s.feat, sizeof(psift_feature) * (size_t)n_ext, cudaMemcpyDeviceToHost, s.stream ) );
-            CU( cudaMemcpyAsync( s.h_ext,  s.ext,  sizeof(psift_extremum) * (size_t)n_ext, cudaMemcpyDeviceToHost, s.stream ) );
+        if( n_ext > s.run_pre_ext || n_desc > s.run_pre_desc ) {
+            /* more results than the frame downloaded by itself: fetch them all (the host buffers may have to grow) */
+            int rc = ensure_host_results( s, n_ext, n_desc );
+            if( rc ) return rc;
+            if( n_ext > 0 ) {
+                CU( cudaMemcpyAsync( s.h_feat, s.feat, sizeof(psift_feature) * (size_t)n_ext, cudaMemcpyDeviceToHost, s.stream ) );
+                CU( cudaMemcpyAsync( s.h_ext,  s.ext,  sizeof(psift_extremum) * (size_t)n_ext, cudaMemcpyDeviceToHost, s.stream ) );
+            }
+            if( n_desc > 0 )
+                CU( cudaMemcpyAsync( s.h_desc, s.desc, sizeof(float) * 128 * (size_t)n_desc, cudaMemcpyDeviceToHost, s.stream ) );
+            c->d2h_bytes += (long long)n_ext * ( sizeof(psift_feature) + sizeof(psift_extremum) ) + (long long)n_desc * 512;
         }
-        if( n_desc > 0 )
-            CU( cudaMemcpyAsync( s.h_desc, s.desc, sizeof(float) * 128 * (size_t)n_desc, cudaMemcpyDeviceToHost, s.stream ) );
         CU( cudaEventRecord( s.ev[6], s.stream ) );
         CU( cudaStreamSynchronize( s.stream ) );
         j->waited = true;
+        /* size the next frames' own download from what this one produced */
+        const int want_ext  = std::min( s.ext_cap,  ( n_ext  + n_ext  / 4 + 1023 ) / 1024 * 1024 );
+        const int want_desc = std::min( s.desc_cap, ( n_desc + n_desc / 4 + 1023 ) / 1024 * 1024 );
+        if( want_ext > s.pre_ext || want_desc > s.pre_desc ) {
+            s.pre_ext = std::max( s.pre_ext, want_ext ); s.pre_desc = std::max( s.pre_desc, want_desc );
+            s.epoch++;
+        }
         std::lock_guard<std::mutex> lk( c->mu );
         float ms = 0.f;
         for( int k = 0; k < 6; k++ ) { if( cudaEventElapsedTime( &ms, s.ev[k], s.ev[k + 1] ) == cudaSuccess ) c->last_ms[k] = ms; }
@@ -913,6 +939,7 @@ int psift_last_level_timing( psift_ctx* c, float* ms, int cap, int* n )
 }
 
 long long psift_launch_count( psift_ctx* c ) { return c ? c->launches : 0; }
+long long psift_d2h_bytes( psift_ctx* c ) { return c ? c->d2h_bytes : 0; }
 
 int psift_debug_mark( psift_ctx* c, int which )
 {
