@@ -82,6 +82,25 @@ def test_deterministic_and_slot_independent():
         assert a.desc.tobytes() == b.desc.tobytes()
 
 
+def test_graph_replay_and_result_prefix():
+    """A frame slot replays its frame as a CUDA graph from the second use on, and the graph downloads a result prefix
+    sized from earlier frames: results must not depend on what the slot saw before (first use, replay, a poorer image
+    in between, then a richer one than any prefix, same size so the graph is reused)."""
+    rich, poor = load("g640"), synth.single_blob(640, 480, 300.5, 200.25, 5.0)
+    with capi.Context(capi.default_config()) as ctx:
+        first = ctx.extract(rich)
+    with capi.Context(capi.default_config()) as ctx:
+        seq = []
+        for im in [poor] * 8 + [rich] * 8 + [poor] * 7 + [rich] * 7:      # every slot sees both, in both orders
+            seq.append((im is rich, ctx.extract(im)))
+    blob = [r for is_rich, r in seq if not is_rich]
+    assert all(r.n_feat == blob[0].n_feat and r.feat.tobytes() == blob[0].feat.tobytes() and r.desc.tobytes() == blob[0].desc.tobytes() for r in blob)
+    for is_rich, r in seq:
+        if is_rich:
+            assert r.n_feat == first.n_feat and r.n_desc == first.n_desc
+            assert r.feat.tobytes() == first.feat.tobytes() and r.ext.tobytes() == first.ext.tobytes() and r.desc.tobytes() == first.desc.tobytes()
+
+
 def test_device_resident_input_equals_host_input():
     import torch
     img = load("g640")
