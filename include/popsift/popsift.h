@@ -91,6 +91,11 @@ public:
     /* extensions */
     int  deviceCount() const;                 /* GPUs this object dispatches to */
     static void setDeviceLimit( int n );      /* use at most n GPUs (0 = all); call before constructing */
+    /* One giant image cut into row bands over all GPUs of this object (the reference runs such an
+     * image un-tiled on one GPU): synchronous, returns the merged features, identical to the un-tiled result.  Uses its
+     * own contexts (created on first use), so it may be called while enqueue()d jobs are in flight.  The caller owns
+     * the result.  bands = 0: one band per GPU. */
+    popsift::FeaturesHost* extractTiled( int w, int h, const unsigned char* imageData, int bands = 0 );
 
 private:
     PopSiftImpl*    _impl;

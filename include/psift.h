@@ -202,6 +202,19 @@ int  psift_band_seed_copy( psift_job* job, float* dst_dev, size_t dst_pitch_byte
 int  psift_submit_seed_dev_f32( psift_ctx* ctx, int w, int h, int first_octave, const float* dev_plane, size_t pitch_bytes,
                                 int y0, int y1, psift_job** out );
 
+/* The whole of the above in one call: band pass on every context, exchange of the seed rows (device-to-device; peer
+ * copies over NVLink between GPUs), seeded pass, merge.  ctxs: n_ctx contexts with the SAME configuration, normally one
+ * per GPU (several on one GPU work too).  The result arrays are malloc'ed: psift_banded_free. */
+typedef struct psift_banded_result {
+    int n_feat, n_desc, split_octave;
+    psift_feature*  feat;
+    psift_extremum* ext;
+    float*          desc;
+} psift_banded_result;
+int  psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8_t* host_img, size_t pitch,
+                           int max_seed_pixels, psift_banded_result* out );
+void psift_banded_free( psift_banded_result* r );
+
 /* Device-side stopwatch over everything queued on the context between two marks: mark 0 is
  * stamped once all work queued so far has finished, mark 1 likewise; elapsed() waits for mark 1
  * and returns the CUDA-event time between them.  bench.py times its K steps with it. */

@@ -41,6 +41,12 @@ DESC = {"loop": 0, "iloop": 1, "grid": 2, "igrid": 3, "notile": 4}
 NORM = {"RootSift": 0, "classic": 1}
 FSORT = {"random": 0, "down": 1, "up": 2}   # reference sift_conf.cu:131-141 (up = smallest scale first)
 
+class BandedResult(C.Structure):
+    """psift_banded_result (psift.h)"""
+    _fields_ = [("n_feat", C.c_int), ("n_desc", C.c_int), ("split_octave", C.c_int),
+                ("feat", C.c_void_p), ("ext", C.c_void_p), ("desc", C.c_void_p)]
+
+
 class DevInfo(C.Structure):
     """psift_dev_info (psift.h)"""
     _fields_ = [("device", C.c_int), ("n_feat", C.c_int), ("n_desc", C.c_int),
@@ -52,7 +58,7 @@ EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "ps
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
            "psift_launch_count", "psift_d2h_bytes", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",
-           "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32",
+           "psift_extract_banded", "psift_banded_free", "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32",
            "psift_wait_dev", "psift_dev_features_alloc", "psift_dev_features_free", "psift_dev_features_info", "psift_match",
            "psift_match_dev", "psift_dev_download", "psift_dev_upload"]
 
@@ -91,6 +97,9 @@ def lib():
         L.psift_band_seed_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int]
         L.psift_submit_seed_dev_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.psift_debug_mark.argtypes = [C.c_void_p, C.c_int]
+        L.psift_extract_banded.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.POINTER(BandedResult)]
+        L.psift_banded_free.argtypes = [C.POINTER(BandedResult)]
+        L.psift_banded_free.restype = None
         L.psift_debug_time_levels.argtypes = [C.c_void_p, C.c_int]
         L.psift_last_level_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_int)]
         L.psift_wait_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
@@ -312,6 +321,31 @@ def band_plan(cfg, w, h, parts, max_seed_pixels=0):
     split = C.c_int(); b = (C.c_int * (parts + 1))()
     _chk(lib().psift_band_plan(C.byref(cfg), w, h, parts, max_seed_pixels, C.byref(split), b))
     return split.value, [int(v) for v in b]
+
+
+class BandedExtraction:
+    """Result of extract_banded: same fields as Extraction / banded.Merged (feat, ext, desc, n_feat, n_desc)."""
+    def __init__(self, r):
+        self.n_feat, self.n_desc, self.split = r.n_feat, r.n_desc, r.split_octave
+        def arr(ptr, n, dt):
+            if n == 0: return np.zeros(0, dt)
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), (n * dt.itemsize,)).view(dt).copy()
+        self.feat = arr(r.feat, r.n_feat, FEATURE_DTYPE)
+        self.ext = arr(r.ext, r.n_feat, EXTREMUM_DTYPE)
+        self.desc = arr(r.desc, r.n_desc * 128, np.dtype("<f4")).reshape(-1, 128) if r.n_desc else np.zeros((0, 128), np.float32)
+
+
+def extract_banded(contexts, img, max_seed_pixels=0):
+    """One giant image over several contexts (psift_extract_banded): band pass, seed exchange, upper octaves, merge."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    hs = (C.c_void_p * len(contexts))(*[c._h for c in contexts])
+    r = BandedResult()
+    _chk(lib().psift_extract_banded(hs, len(contexts), w, h, img.ctypes.data, w, max_seed_pixels, C.byref(r)))
+    try:
+        return BandedExtraction(r)
+    finally:
+        lib().psift_banded_free(C.byref(r))
 
 
 def geometry(cfg, w, h):

@@ -68,6 +68,9 @@ struct PopSiftImpl
     bool                    started = false;
     std::atomic<long>       processed{ 0 };
     std::vector<psift_ctx*> ctx;
+    std::vector<psift_ctx*> tiled_ctx;                     /* extractTiled()'s own contexts, band r on tiled_ctx[r] */
+    psift_config            tiled_cfg;                     /* what they were last configured with */
+    std::mutex              tiled_mu;
     std::vector<std::thread> workers;
     psift_config            cfg;
     bool                    matching = false;              /* Config::MatchingMode: results stay on the device */
@@ -226,7 +229,39 @@ void PopSift::uninit( )
     I->workers.clear();
     for( auto c : I->ctx ) psift_destroy( c );
     I->ctx.clear();
+    { std::lock_guard<std::mutex> lk( I->tiled_mu ); for( auto c : I->tiled_ctx ) psift_destroy( c ); I->tiled_ctx.clear(); }
     I->started = false;
+}
+
+FeaturesHost* PopSift::extractTiled( int w, int h, const unsigned char* imageData, int bands )
+{
+    PopSiftImpl* I = _impl;
+    if( !I->started || !imageData ) { std::cerr << "popsift: extractTiled on an uninitialised PopSift object" << std::endl; return new FeaturesHost( 0, 0 ); }
+    std::lock_guard<std::mutex> lk( I->tiled_mu );
+    const int n_dev = (int)I->ctx.size();
+    const int n = bands > 0 ? bands : n_dev;
+    if( !I->tiled_ctx.empty() && memcmp( &I->tiled_cfg, &I->cfg, sizeof I->cfg ) != 0 )
+        for( auto c : I->tiled_ctx ) psift_configure( c, &I->cfg );   /* follow configure() */
+    I->tiled_cfg = I->cfg;
+    while( (int)I->tiled_ctx.size() < n ) {
+        psift_ctx* c = 0;
+        if( psift_create( (int)I->tiled_ctx.size() % n_dev, &I->cfg, &c ) != PSIFT_OK ) {
+            std::cerr << "popsift: cannot create a context for a band: " << psift_last_error() << std::endl;
+            return new FeaturesHost( 0, 0 );
+        }
+        I->tiled_ctx.push_back( c );
+    }
+    psift_banded_result r;
+    if( psift_extract_banded( I->tiled_ctx.data(), n, w, h, imageData, 0, 0, &r ) != PSIFT_OK ) {
+        std::cerr << "popsift: tiled extraction failed: " << psift_last_error() << std::endl;
+        return new FeaturesHost( 0, 0 );
+    }
+    psift_result pr;
+    memset( &pr, 0, sizeof pr );
+    pr.n_feat = r.n_feat; pr.n_desc = r.n_desc; pr.feat = r.feat; pr.desc = r.desc; pr.ext = r.ext;
+    FeaturesHost* fh = PopSiftImpl::convert( pr );
+    psift_banded_free( &r );
+    return fh;
 }
 
 SiftJob* PopSift::enqueue( int w, int h, const unsigned char* imageData )

@@ -801,7 +801,7 @@ int psift_band_seed_copy( psift_job* j, float* dst_dev, size_t dst_pitch_bytes, 
     if( row_from < L.row_lo[o] || row_to > L.row_hi[o] || row_to <= row_from ) return fail( PSIFT_E_INVALID, "rows [%d,%d) outside the band's seed rows [%d,%d)", row_from, row_to, L.row_lo[o], L.row_hi[o] );
     CU( cudaSetDevice( j->ctx->device ) );
     CU( cudaMemcpy2DAsync( dst_dev, dst_pitch_bytes, L.base[o] + (size_t)row_from * L.pitch[o], (size_t)L.pitch[o] * 4,
-                           (size_t)L.w[o] * 4, row_to - row_from, cudaMemcpyDeviceToDevice, s.stream ) );
+                           (size_t)L.w[o] * 4, row_to - row_from, cudaMemcpyDefault, s.stream ) );   /* dst may live on another GPU */
     CU( cudaStreamSynchronize( s.stream ) );
     return PSIFT_OK;
 }
@@ -1087,6 +1087,102 @@ int psift_dev_upload( int device, void* dev, const void* host, size_t bytes )
     CU( cudaSetDevice( device ) );
     CU( cudaMemcpy( dev, host, bytes, cudaMemcpyHostToDevice ) );
     return PSIFT_OK;
+}
+
+/* One giant image over the given contexts (one per GPU; several on one GPU work too), start to finish:
+ * band pass on every context, the ONE exchange step (every band's rows of the seed plane go to every context's copy of
+ * it: peer copies over NVLink between different GPUs), seeded pass for the octaves above the split, results merged. */
+namespace {
+struct BandedParts {
+    std::vector<psift_feature> feat; std::vector<psift_extremum> ext; std::vector<float> desc;
+    void add( const psift_result& r )
+    {
+        const int nd0 = (int)( desc.size() / 128 );
+        for( int i = 0; i < r.n_feat; i++ ) {
+            psift_feature f = r.feat[i]; psift_extremum e = r.ext[i];
+            for( int k = 0; k < PSIFT_MAX_ORI; k++ ) if( f.desc_idx[k] >= 0 ) f.desc_idx[k] += nd0;
+            e.idx_ori += nd0;
+            feat.push_back( f ); ext.push_back( e );
+        }
+        desc.insert( desc.end(), r.desc, r.desc + (size_t)r.n_desc * 128 );
+    }
+};
+}
+
+int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8_t* host_img, size_t pitch,
+                          int max_seed_pixels, psift_banded_result* out )
+{
+    if( !ctxs || n_ctx < 1 || !host_img || !out ) return fail( PSIFT_E_INVALID, "null argument" );
+    memset( out, 0, sizeof *out );
+    for( int r = 0; r < n_ctx; r++ ) if( !ctxs[r] ) return fail( PSIFT_E_INVALID, "null context" );
+    const psift_config cfg = ctxs[0]->cfg;
+    const int n_oct = octave_count( cfg, w, h );
+    int split = 0;
+    std::vector<int> bounds( n_ctx + 1, 0 );
+    int rc = psift_band_plan( &cfg, w, h, n_ctx, max_seed_pixels, &split, bounds.data() );
+    if( rc ) return rc;
+    out->split_octave = split;
+
+    BandedParts P;
+    std::vector<psift_job*> jobs( n_ctx, nullptr );
+    std::vector<float*> plane( n_ctx, nullptr );
+    auto cleanup = [&]() {
+        for( int r = 0; r < n_ctx; r++ ) {
+            if( jobs[r] ) { psift_job_free( jobs[r] ); jobs[r] = nullptr; }
+            if( plane[r] ) { cudaSetDevice( ctxs[r]->device ); cudaFree( plane[r] ); plane[r] = nullptr; }
+        }
+    };
+    /* band pass: all contexts work at the same time */
+    for( int r = 0; r < n_ctx; r++ )
+        if( ( rc = psift_submit_band_u8( ctxs[r], w, h, host_img, pitch, 0, bounds[r], bounds[r + 1], split, &jobs[r] ) ) != PSIFT_OK ) { cleanup(); return rc; }
+    for( int r = 0; r < n_ctx; r++ ) {
+        psift_result res;
+        if( ( rc = psift_wait( jobs[r], &res ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        P.add( res );
+    }
+    if( split + 1 < n_oct ) {
+        int sw = 0, sh = 0;
+        const float* rows; int pf, lo, hi;
+        if( ( rc = psift_band_seed( jobs[0], &rows, &pf, &lo, &hi, &sw, &sh ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        for( int r = 0; r < n_ctx; r++ ) {
+            cudaSetDevice( ctxs[r]->device );
+            for( int q = 0; q < n_ctx; q++ )                         /* peer access where the hardware has it; else the copy is staged */
+                if( ctxs[q]->device != ctxs[r]->device ) { cudaDeviceEnablePeerAccess( ctxs[q]->device, 0 ); cudaGetLastError(); }
+            if( cudaMalloc( &plane[r], sizeof(float) * (size_t)sw * sh ) != cudaSuccess ) { cleanup(); return fail( PSIFT_E_CUDA, "seed plane: out of memory" ); }
+        }
+        /* the exchange: band r's own rows of the seed plane -> every context's plane */
+        for( int r = 0; r < n_ctx; r++ ) {
+            const int a = bounds[r] >> ( split + 1 );
+            const int b = ( r + 1 == n_ctx ) ? sh : std::min( sh, bounds[r + 1] >> ( split + 1 ) );
+            if( b <= a ) continue;
+            for( int q = 0; q < n_ctx; q++ )
+                if( ( rc = psift_band_seed_copy( jobs[r], plane[q] + (size_t)a * sw, (size_t)sw * 4, a, b ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        }
+        for( int r = 0; r < n_ctx; r++ ) { psift_job_free( jobs[r] ); jobs[r] = nullptr; }
+        for( int r = 0; r < n_ctx; r++ )
+            if( ( rc = psift_submit_seed_dev_f32( ctxs[r], w, h, split + 1, plane[r], (size_t)sw * 4, bounds[r], bounds[r + 1], &jobs[r] ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        for( int r = 0; r < n_ctx; r++ ) {
+            psift_result res;
+            if( ( rc = psift_wait( jobs[r], &res ) ) != PSIFT_OK ) { cleanup(); return rc; }
+            P.add( res );
+        }
+    }
+    cleanup();
+    out->n_feat = (int)P.feat.size(); out->n_desc = (int)( P.desc.size() / 128 );
+    out->feat = (psift_feature*)malloc( sizeof(psift_feature) * std::max<size_t>( P.feat.size(), 1 ) );
+    out->ext  = (psift_extremum*)malloc( sizeof(psift_extremum) * std::max<size_t>( P.ext.size(), 1 ) );
+    out->desc = (float*)malloc( sizeof(float) * std::max<size_t>( P.desc.size(), 1 ) );
+    if( !out->feat || !out->ext || !out->desc ) { psift_banded_free( out ); return fail( PSIFT_E_INVALID, "out of host memory" ); }
+    if( !P.feat.empty() ) { memcpy( out->feat, P.feat.data(), sizeof(psift_feature) * P.feat.size() ); memcpy( out->ext, P.ext.data(), sizeof(psift_extremum) * P.ext.size() ); }
+    if( !P.desc.empty() ) memcpy( out->desc, P.desc.data(), sizeof(float) * P.desc.size() );
+    return PSIFT_OK;
+}
+
+void psift_banded_free( psift_banded_result* r )
+{
+    if( !r ) return;
+    free( r->feat ); free( r->ext ); free( r->desc );
+    memset( r, 0, sizeof *r );
 }
 
 } // extern "C"

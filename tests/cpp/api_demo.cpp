@@ -16,13 +16,14 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <cmath>
 #include <sstream>
 
 int main( int argc, char** argv )
 {
     if( argc < 5 ) { fprintf( stderr, "usage: api_demo in.u8 w h out.bin [repeat] [flags]\n" ); return 2; }
     const int w = atoi( argv[2] ), h = atoi( argv[3] );
-    int repeat = 1, a = 5;
+    int repeat = 1, a = 5, tiled = 0;
     if( argc > 5 && argv[5][0] != '-' ) { repeat = atoi( argv[5] ); a = 6; }
 
     popsift::Config config;
@@ -34,6 +35,7 @@ int main( int argc, char** argv )
         else if( k == "--norm-multi" ) config.setNormalizationMultiplier( atoi( v.c_str() ) );
         else if( k == "--downsampling" ) config.setDownsampling( (float)atof( v.c_str() ) );
         else if( k == "--levels" ) config.setLevels( atoi( v.c_str() ) );
+        else if( k == "--tiled" ) tiled = atoi( v.c_str() );
         else if( k == "--mode" ) config.setMode( v == "vlfeat" ? popsift::Config::VLFeat : v == "opencv" ? popsift::Config::OpenCV : popsift::Config::PopSift );
         else { fprintf( stderr, "unknown flag %s\n", k.c_str() ); return 2; }
     }
@@ -50,6 +52,7 @@ int main( int argc, char** argv )
 
     std::vector<SiftJob*> jobs;
     for( int i = 0; i < repeat; i++ ) jobs.push_back( sift.enqueue( w, h, img.data() ) );
+    const std::vector<unsigned char> keep( img );
     std::fill( img.begin(), img.end(), 0 );          /* the job owns a private copy */
 
     popsift::Features* last = 0;
@@ -65,6 +68,21 @@ int main( int argc, char** argv )
     }
     fprintf( stderr, "Number of feature points: %d, number of feature descriptors: %d, GPUs: %d\n",
              last->getFeatureCount(), last->getDescriptorCount(), sift.deviceCount() );
+
+    if( tiled > 0 ) {
+        /* the same image cut into row bands (PopSift::extractTiled): the same keypoints, in another order */
+        popsift::Features* t = sift.extractTiled( w, h, keep.data(), tiled );
+        if( t->getFeatureCount() != last->getFeatureCount() || t->getDescriptorCount() != last->getDescriptorCount() ) {
+            fprintf( stderr, "tiled: %d/%d features/descriptors, un-tiled %d/%d\n", t->getFeatureCount(), t->getDescriptorCount(), last->getFeatureCount(), last->getDescriptorCount() );
+            return 5;
+        }
+        double sa[4] = { 0, 0, 0, 0 }, sb[4] = { 0, 0, 0, 0 };
+        for( popsift::Features::F_const_iterator it = last->begin(); it != last->end(); ++it ) { sa[0] += it->xpos; sa[1] += it->ypos; sa[2] += it->sigma; for( int k = 0; k < it->num_ori; k++ ) for( int q = 0; q < 128; q++ ) sa[3] += it->desc[k]->features[q]; }
+        for( popsift::Features::F_const_iterator it = t->begin(); it != t->end(); ++it )       { sb[0] += it->xpos; sb[1] += it->ypos; sb[2] += it->sigma; for( int k = 0; k < it->num_ori; k++ ) for( int q = 0; q < 128; q++ ) sb[3] += it->desc[k]->features[q]; }
+        for( int k = 0; k < 4; k++ ) if( fabs( sa[k] - sb[k] ) > 1e-6 * ( 1.0 + fabs( sa[k] ) ) ) { fprintf( stderr, "tiled: checksum %d differs (%.9g vs %.9g)\n", k, sb[k], sa[k] ); return 6; }
+        fprintf( stderr, "tiled in %d bands: identical keypoint set\n", tiled );
+        delete t;
+    }
 
     FILE* o = fopen( argv[4], "wb" );
     int hdr[2] = { last->getFeatureCount(), last->getDescriptorCount() };

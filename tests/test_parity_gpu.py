@@ -205,6 +205,16 @@ def test_cpp_api_demo_matches_golden(tmp_path):
     assert d < parity.TOL_DESC
 
 
+def test_cpp_extract_tiled(tmp_path):
+    """PopSift::extractTiled: the giant-image mode through the C++ class (three bands on the GPUs present)."""
+    exe = os.path.join(ROOT, "tests", "cpp", "api_demo")
+    if not os.path.exists(exe): pytest.skip("tests/cpp/api_demo not built")
+    w, h, _ = gc.IMAGES["g640"]
+    r = subprocess.run([exe, gc.image_path("g640"), str(w), str(h), str(tmp_path / "t.bin"), "1", "--downsampling", "0", "--tiled", "3"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "identical keypoint set" in r.stderr, r.stderr[-800:]
+
+
 ORACLE = os.path.join(ROOT, "oracle", "cpu_sift")
 ORACLE_CASES = [(200, 150, 21, []), (97, 131, 22, []), (320, 240, 23, ["--mode", "vlfeat", "--desc-mode", "grid"]),
                 (161, 243, 24, ["--downsampling", "0", "--norm-mode", "classic"]), (128, 128, 25, ["--mode", "opencv", "--gauss-mode", "opencv"]),
@@ -270,6 +280,29 @@ def test_banded_equals_whole(w, h, parts, seed_px, flags):
     ka, da = _canon(tiled); kb, db = _canon(whole)
     assert ka == kb
     assert da == db
+
+
+def test_extract_banded_one_call():
+    """psift_extract_banded (three contexts on this GPU; on a multi-GPU box they would be one per GPU and the seed rows
+    would travel as peer copies): the merged keypoints equal the un-split run's, record for record."""
+    img = synth.gen(1024, 768, 7)
+    cfg = capi.default_config(downsampling=0)
+    with capi.Context(cfg) as ctx:
+        whole = ctx.extract(img)
+    ctxs = [capi.Context(cfg) for _ in range(3)]
+    try:
+        got = capi.extract_banded(ctxs, img, max_seed_pixels=128 * 96)
+    finally:
+        for c in ctxs: c.close()
+    assert got.split >= 1 and got.n_feat == whole.n_feat and got.n_desc == whole.n_desc
+    def canon(ex):
+        o = np.lexsort((ex.feat["x"], ex.feat["y"], ex.feat["sigma"], ex.feat["octave"]))
+        f = ex.feat[o]
+        d = np.stack([ex.desc[f["desc_idx"][:, k].clip(0)] * (f["desc_idx"][:, k:k + 1] >= 0) for k in range(4)], 1)
+        rec = [f[n].tobytes() for n in ("octave", "x", "y", "sigma", "num_ori", "ori")]
+        return rec, d.tobytes()
+    a, b = canon(got), canon(whole)
+    assert a[0] == b[0] and a[1] == b[1]
 
 
 def test_keypoint_buffers_grow():
