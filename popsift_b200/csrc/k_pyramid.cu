@@ -398,7 +398,10 @@ k_blur2( const __grid_constant__ BlurArgs a )
  * Measured (B200, a 3840x2160 level, ncu with flushed caches): 19.8 ... 32.6 us for 11 ... 27 taps against 23.0 ...
  * 43.1 us for k_blur2.  What bounds it (profiles/r01d_ncu_blur_march.txt): a step of the 11-tap level is 176 packed
  * FFMA2/FADD2 (two issue cycles each) plus about 250 other instructions for 512 pixels, so the issue slots, not HBM
- * (66 MB in 20 us = 3.3 TB/s), set the time; more warps per SM do not help (8 and 16 were measured equal).
+ * (66 MB in 20 us = 3.3 TB/s), set the time; more warps per SM do not help (8, 12 and 16 were measured equal, also with
+ * the registers capped for 3 blocks per SM), and neither did taking 15 % of the non-FMA instructions out of the common
+ * step (the unclamped staging / plain-store paths below).  Over the five tap counts the time fits
+ * 12.5 us + 2.8 cycles per packed instruction and scheduler: the packed FMA pipe is the slope, the constant is next.
  * ------------------------------------------------------------------------------------------ */
 constexpr int MW     = 64;       /* strip width (columns per warp) */
 constexpr int MWARPS = 4;        /* warps per block; they do not cooperate */
@@ -490,6 +493,20 @@ k_blur_march( const __grid_constant__ MarchArgs m )
     float tq[FROM_TEX ? NRP : 1][FROM_TEX ? NK : 1];
     auto request = [&]( int q ) {
         float* sb = reinterpret_cast<float*>( S4 + ( q % NB ) * SBUF ) + sbase;
+        const int row_first = r0 - H + q * RS;
+        if( !FROM_TEX && !edge && row_first >= a.y_lo && row_first + RS <= a.y_hi ) {
+            /* the common step: no clamping anywhere, one row pointer and constant offsets */
+            const float* gr = a.src + (long long)( row_first + hp ) * a.pitch + gx0;
+            #pragma unroll
+            for( int rp = 0; rp < NRP; rp++ ) {
+                float* sr = sb + rp * RPB * 4;
+                #pragma unroll
+                for( int k = 0; k < NK; k++ )
+                    if( 16 * k + 15 < SW || hl + 16 * k < SW ) cp_async4( sr + ( 32 / M ) * k, gr + 16 * k );
+                gr += 2 * a.pitch;
+            }
+            return;
+        }
         #pragma unroll
         for( int rp = 0; rp < NRP; rp++ ) {
             const int g = min( max( r0 - H + q * RS + 2 * rp + hp, a.y_lo ), a.y_hi - 1 );
@@ -611,12 +628,25 @@ k_blur_march( const __grid_constant__ MarchArgs m )
             const int rowb = r0 - 2 * H + s * RS;        /* output row of j = 0; even, like r0 */
             float* q  = a.dst + (long long)rowb * a.pitch + gxo;
             float* qd = a.ds_dst + (long long)( rowb >> 1 ) * a.ds_pitch + ( gxo >> 1 );
-            const bool okx = gxo < w, okd = okx && a.ds_dst != nullptr;
-            #pragma unroll
-            for( int j = 0; j < RS; j++ ) {
-                const bool ok = (unsigned)( rowb + j - r0 ) < (unsigned)( r1 - r0 );
-                st_pred_v2( q + (long long)j * a.pitch, acc[j], ok && okx );
-                if( ( j & 1 ) == 0 ) st_pred( qd + (long long)( j >> 1 ) * a.ds_pitch, acc[j].x, ok && okd );
+            if( rowb >= r0 && rowb + RS <= r1 && x0 + MW <= w ) {
+                /* the common step: all RS rows and all 64 columns exist, plain stores off two running pointers */
+                #pragma unroll
+                for( int j = 0; j < RS; j++ ) {
+                    *reinterpret_cast<float2*>( q ) = acc[j];
+                    q += a.pitch;
+                }
+                if( a.ds_dst ) {
+                    #pragma unroll
+                    for( int j = 0; j < RS; j += 2 ) { *qd = acc[j].x; qd += a.ds_pitch; }
+                }
+            } else {
+                const bool okx = gxo < w, okd = okx && a.ds_dst != nullptr;
+                #pragma unroll
+                for( int j = 0; j < RS; j++ ) {
+                    const bool ok = (unsigned)( rowb + j - r0 ) < (unsigned)( r1 - r0 );
+                    st_pred_v2( q + (long long)j * a.pitch, acc[j], ok && okx );
+                    if( ( j & 1 ) == 0 ) st_pred( qd + (long long)( j >> 1 ) * a.ds_pitch, acc[j].x, ok && okd );
+                }
             }
         }
     }
