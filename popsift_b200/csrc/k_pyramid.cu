@@ -408,7 +408,7 @@ constexpr int MWARPS = 4;        /* warps per block; they do not cooperate */
 
 struct MarchArgs {
     BlurArgs b;
-    int nstrip, nseg, seg_rows;  /* seg_rows: multiple of RS */
+    int nstrip, nseg, seg_rows;  /* seg_rows: even */
 };
 
 __device__ __forceinline__ void cp_async4( void* smem_dst, const void* gsrc )
@@ -679,9 +679,18 @@ static cudaError_t launch_march_rs( const BlurArgs& a, cudaStream_t st )
     MarchArgs m; m.b = a;
     const int rows = a.y_hi - a.y_lo;
     m.nstrip = ( a.w + MW - 1 ) / MW;
-    int nseg = std::max( 1, sms * march_wps() / m.nstrip );
-    m.seg_rows = std::max( 32, ( ( rows + nseg - 1 ) / nseg + RS - 1 ) / RS * RS );
-    m.nseg = ( rows + m.seg_rows - 1 ) / m.seg_rows;
+    /* segments per strip: about march_wps() warps per SM, picked among the neighbouring counts for the fewest steps of
+     * the slowest SM (steps of a segment, RS rows each, 2H of warm-up) x (blocks on the fullest SM).  Segments start on
+     * even rows (the fused downscale takes even rows). */
+    const int target = std::max( 1, sms * march_wps() / m.nstrip );
+    long best = -1;
+    for( int n = std::max( 1, target - 3 ); n <= target + 3; n++ ) {
+        const int sr = std::max( 32, ( ( rows + n - 1 ) / n + 1 ) / 2 * 2 );
+        const int ns = ( rows + sr - 1 ) / sr;
+        const int bl = ( m.nstrip * ns + MWARPS - 1 ) / MWARPS;
+        const long cost = (long)( ( sr + 2 * H + RS - 1 ) / RS ) * ( ( bl + sms - 1 ) / sms );
+        if( best < 0 || cost < best ) { best = cost; m.seg_rows = sr; m.nseg = ns; }
+    }
     const int blocks = ( m.nstrip * m.nseg + MWARPS - 1 ) / MWARPS;
     return launch_pdl( k_blur_march<H, RS, FROM_TEX>, dim3( blocks ), dim3( 32 * MWARPS ), smem, st, m );
 }
