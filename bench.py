@@ -26,8 +26,8 @@ W, H = 1920, 1080
 BATCH = 25            # frames per step per GPU
 N_DISTINCT = 16       # distinct synthetic frames cycled through (seeds 1000..1015)
 IN_FLIGHT = int(os.environ.get("PSIFT_SLOTS", "6"))   # frames in flight = frame slots of the context
-BLUR_DRAM_BYTES = 33.7e6       # dram read+write of one k_blur_march launch (3840x2160 level), ncu --set full: profiles/r01d_ncu_blur_march.txt
-PROFILE_SRC = "profiles/r01d_ncu_blur_march.txt"
+BLUR_DRAM_BYTES = 33.7e6       # dram read+write of one k_blur_march launch (3840x2160 level), ncu --set full: profiles/r01f_ncu_blur_march.txt
+PROFILE_SRC = "profiles/r01f_ncu_blur_march.txt"
 N_PYR_LAUNCHES = 46
 
 
