@@ -23,6 +23,11 @@
 using popsift::FeaturesHost;
 using popsift::FeaturesBase;
 
+namespace popsift {
+/* host/debug_dump.cpp: Config::LogMode::All */
+void debug_dump_all( void* ctx, const Config& conf, int n_octaves, int n_levels, FeaturesHost* features, const char* basename );
+}
+
 /* ------------------------------------------------------------------ SiftJob */
 
 SiftJob::SiftJob( int w, int h, const unsigned char* imageData )
@@ -73,6 +78,7 @@ struct PopSiftImpl
     std::mutex              tiled_mu;
     std::vector<std::thread> workers;
     psift_config            cfg;
+    popsift::Config         conf;                          /* as configured (log mode, upscale factor for the debug dumps) */
     bool                    matching = false;              /* Config::MatchingMode: results stay on the device */
     static const int        IN_FLIGHT = 3;
 
@@ -145,6 +151,8 @@ void PopSiftImpl::worker( int idx )
         } else if( psift_wait( pj, &r ) == PSIFT_OK ) {
             fh = convert( r );
             if( r.n_desc == 0 && r.n_feat != 0 ) std::cerr << "Warning: no descriptors extracted" << std::endl;
+            if( conf.getLogMode() == popsift::Config::All )          /* popsift.cpp:201-209; the planes are still in the slot */
+                popsift::debug_dump_all( c, conf, r.n_octaves, r.n_levels, static_cast<FeaturesHost*>( fh ), "pyramid" );
         } else {
             std::cerr << "popsift: extraction failed: " << psift_last_error() << std::endl;
             fh = new FeaturesHost( 0, 0 );
@@ -181,6 +189,7 @@ bool PopSift::configure( const popsift::Config& config, bool force )
     _config = config;
     _config.levels = std::max( 2, config.levels );                   /* popsift.cpp:71 */
     _config.toC( &I->cfg );
+    I->conf = _config;
     if( I->ctx.empty() ) {
         int n = psift_device_count();
         const char* env = getenv( "POPSIFT_NUM_GPUS" );

@@ -36,6 +36,7 @@ int main( int argc, char** argv )
         else if( k == "--downsampling" ) config.setDownsampling( (float)atof( v.c_str() ) );
         else if( k == "--levels" ) config.setLevels( atoi( v.c_str() ) );
         else if( k == "--tiled" ) tiled = atoi( v.c_str() );
+        else if( k == "--log" ) config.setLogMode( v == "all" ? popsift::Config::All : popsift::Config::None );
         else if( k == "--mode" ) config.setMode( v == "vlfeat" ? popsift::Config::VLFeat : v == "opencv" ? popsift::Config::OpenCV : popsift::Config::PopSift );
         else { fprintf( stderr, "unknown flag %s\n", k.c_str() ); return 2; }
     }

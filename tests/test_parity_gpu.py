@@ -205,6 +205,42 @@ def test_cpp_api_demo_matches_golden(tmp_path):
     assert d < parity.TOL_DESC
 
 
+def test_log_mode_all_dumps(tmp_path):
+    """Config::LogMode::All through the C++ class: the reference's debug files (sift_octave.cu:110-187, sift_pyramid.cu:88-106)
+    in its formats; the float dumps must hold exactly the planes of the reference's own run."""
+    exe = os.path.join(ROOT, "tests", "cpp", "api_demo")
+    if not os.path.exists(exe): pytest.skip("tests/cpp/api_demo not built")
+    w, h, _ = gc.IMAGES["g64"]
+    r = subprocess.run([exe, gc.image_path("g64"), str(w), str(h), str(tmp_path / "o.bin"), "1", "--log", "all"],
+                       capture_output=True, text=True, timeout=300, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stderr[-800:]
+    ref = refio.RefPlanes(os.path.join(refio.GOLD, "ref", "g64_default.planes.bin"))
+    def dump(path):
+        b = open(path, "rb").read()
+        assert b.startswith(b"floats\n")
+        nl = b.index(b"\n", 7)
+        cols, rows = [int(v) for v in b[7:nl].split()]
+        return np.frombuffer(b, "<f4", cols * rows, nl + 1).reshape(rows, cols)
+    for o in range(ref.n_octaves):
+        for l in range(ref.n_levels):
+            g = dump(tmp_path / "dir-octave-dump" / ("pyramid-o-%d-l-%d.dump" % (o, l)))
+            assert np.array_equal(g.view(np.uint32), ref.gauss[o][l].view(np.uint32))
+        for l in range(ref.n_levels - 1):
+            d = dump(tmp_path / "dir-dog-dump" / ("d-pyramid-o-%d-l-%d.dump" % (o, l)))
+            assert np.array_equal(d.view(np.uint32), ref.dog[o][l].view(np.uint32))
+    # text planes: P2, truncated values (+127 for the DoG text files)
+    t = open(tmp_path / "dir-octave" / "pyramid-o-0-l-0.pgm").read().split()
+    assert t[0] == "P2" and (int(t[1]), int(t[2])) == ref.size[0] and t[3] == "255"
+    assert np.array_equal(np.array(t[4:], np.int64).reshape(ref.size[0][1], ref.size[0][0]), ref.gauss[0][0].astype(np.int64))
+    t = open(tmp_path / "dir-dog-txt" / "d-pyramid-o-0-l-1.txt").read().split()
+    assert np.array_equal(np.array(t[4:], np.int64).reshape(ref.size[0][1], ref.size[0][0]), ref.dog[0][1].astype(np.int64) + 127)
+    assert os.path.exists(tmp_path / "dir-dog" / "d-pyramid-o-0-l-0.pgm")
+    gold = refio.RefFeatures(os.path.join(refio.GOLD, "ref", "g64_default.feat.bin"))
+    lines = open(tmp_path / "dir-desc" / "desc-pyramid.txt").read().strip().split("\n")
+    assert len(lines) == gold.n_desc and all(len(x.split()) == 132 for x in lines)
+    assert len(open(tmp_path / "dir-fpt" / "desc-pyramid.txt").read().strip().split("\n")) == gold.n_desc
+
+
 def test_cpp_extract_tiled(tmp_path):
     """PopSift::extractTiled: the giant-image mode through the C++ class (three bands on the GPUs present)."""
     exe = os.path.join(ROOT, "tests", "cpp", "api_demo")
