@@ -72,7 +72,7 @@ static void parseargs( int argc, char** argv, popsift::Config& config, string& i
         auto fval = [&]() { const string s = val(); char* e; float r = strtof( s.c_str(), &e ); if( *e ) usage_error( "the argument ('" + s + "') for option '" + a + "' is invalid" ); return r; };
         if( a == "-h" || a == "--help" ) { cout << USAGE << '\n'; exit( 1 ); }
         else if( a == "-v" || a == "--verbose" ) config.setVerbose();
-        else if( a == "-l" || a == "--log" ) { config.setLogMode( popsift::Config::All ); cerr << "popsift-demo: --log (debug dumps) is not available in this build" << endl; }
+        else if( a == "-l" || a == "--log" ) config.setLogMode( popsift::Config::All );       /* dir-octave/, dir-dog/, dir-desc/ ... in the working directory */
         else if( a == "-i" || a == "--input-file" ) inputFile = val();
         else if( a == "--octaves" ) config.setOctaves( ival() );
         else if( a == "--levels" ) config.setLevels( ival() );
