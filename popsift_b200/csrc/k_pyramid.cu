@@ -997,18 +997,31 @@ k_fixed_level( const FixedArgs a )
     }
 }
 
+template<bool FROM_TEX> static cudaError_t launch_blur( const BlurArgs& a, cudaStream_t st );
+
 template<int S>
-static cudaError_t launch_pyramid_fixed( const PyrLayout& L, cudaTextureObject_t input_tex, float up_pow, const GaussTables& T,
+static cudaError_t launch_pyramid_fixed( const PyrLayout& L, cudaTextureObject_t input_tex, float up_pow, bool direct_scaling, const GaussTables& T,
                                          cudaStream_t st, long long* launches )
 {
     const int ds_level = L.n_lvl - 3;
     for( int o = L.oct_begin; o < L.oct_end; o++ ) {
+        if( o > 0 && direct_scaling ) {
+            /* ScaleDirect with the fixed modes (s_pyramid_build.cu:478-486): level 0 of the octave comes from the input image
+             * (horizontal dd[o], vertical inc[0]) instead of the previous octave; the levels above it as usual */
+            BlurArgs b;
+            b.w = L.w[o]; b.h = L.h[o]; b.pitch = L.pitch[o]; b.y_lo = L.row_lo[o]; b.y_hi = L.row_hi[o];
+            b.dst = L.base[o]; b.ds_dst = nullptr; b.ds_pitch = 0; b.shift = 0.5f;
+            b.src = nullptr; b.tex = input_tex; b.th = T.dd[o]; b.tv = T.inc[0];
+            cudaError_t e = launch_blur<true>( b, st );
+            if( e != cudaSuccess ) return e;
+            if( launches ) ++*launches;
+        }
         for( int l = ( o == 0 ? 0 : 1 ); l < L.n_lvl; l++ ) {
             FixedArgs a;
             a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
             a.dst = L.base[o] + (size_t)l * L.lstride[o];
             a.ds_dst = nullptr; a.ds_pitch = 0;
-            if( l == ds_level && o + 1 < L.alloc_end ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
+            if( l == ds_level && o + 1 < L.alloc_end && !direct_scaling ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
             a.tshift = 0.5f * up_pow;                               /* s_pyramid_fixed.cu:219 */
             const Taps& t = ( o == 0 ) ? T.abs_o0[l] : T.abs_oN[l];
             for( int i = 0; i < 8; i++ ) a.g[i] = t.g[i];
@@ -1031,8 +1044,8 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
      * input image with the absolute tables (horiz_all + vert_all_abs0, s_pyramid_build.cu:545-548,
      * s_pyramid_build_ra.cu:93-129, s_pyramid_build_aa.cu:133-176); the other octaves are built as usual. */
     if( gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE ) return launch_pyramid_relative( L, input_tex, shift, direct_scaling, T, S, launches );
-    if( gauss_mode == PSIFT_GAUSS_FIXED9 )  return launch_pyramid_fixed<4>( L, input_tex, up_pow, T, S.chain, launches );
-    if( gauss_mode == PSIFT_GAUSS_FIXED15 ) return launch_pyramid_fixed<7>( L, input_tex, up_pow, T, S.chain, launches );
+    if( gauss_mode == PSIFT_GAUSS_FIXED9 )  return launch_pyramid_fixed<4>( L, input_tex, up_pow, direct_scaling, T, S.chain, launches );
+    if( gauss_mode == PSIFT_GAUSS_FIXED15 ) return launch_pyramid_fixed<7>( L, input_tex, up_pow, direct_scaling, T, S.chain, launches );
     /* with ScaleDirect the reference never reaches its vlfeat-direct branch (s_pyramid_build.cu:499 comes first) */
     const bool direct_o0 = gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE_ALL && !direct_scaling;
     const int  ds_level = L.n_lvl - 3;      /* _levels - PREV_LEVEL, s_pyramid_build.cu:229 */

@@ -530,7 +530,6 @@ static int check_config( const psift_config* cfg )
         cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE_ALL && cfg->gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE && !fixed )
         return fail( PSIFT_E_INVALID, "unknown gauss mode %d", cfg->gauss_mode );
     if( cfg->scaling_mode != 0 && cfg->scaling_mode != 1 ) return fail( PSIFT_E_INVALID, "bad scaling mode" );
-    if( fixed && cfg->scaling_mode == 1 ) return fail( PSIFT_E_INVALID, "ScaleDirect is not built for the fixed9/fixed15 Gauss modes" );
     if( fixed && cfg->levels != 3 )           /* s_pyramid_fixed.cu:270-289: "Unsupported number of levels for making all octaves at once" */
         return fail( PSIFT_E_INVALID, "the fixed9/fixed15 Gauss modes need levels = 3 (6 Gaussian levels), as in the reference" );
     if( cfg->desc_mode < 0 || cfg->desc_mode > PSIFT_DESC_NOTILE ) return fail( PSIFT_E_INVALID, "bad desc mode" );

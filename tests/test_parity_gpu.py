@@ -163,7 +163,9 @@ LIVE = [("c1_640x480_default", 640, 480, 1, []),
         ("n4_640x480_relative", 640, 480, 11, ["--gauss-mode", "relative"]),
         ("n4_640x480_scaledirect", 640, 480, 12, ["--scaling", "direct"]),
         ("n4_640x480_scaledirect_relative", 640, 480, 13, ["--scaling", "direct", "--gauss-mode", "relative"]),
-        ("n4_640x480_scaledirect_opencv", 640, 480, 14, ["--scaling", "direct", "--mode", "opencv", "--gauss-mode", "opencv"])]
+        ("n4_640x480_scaledirect_opencv", 640, 480, 14, ["--scaling", "direct", "--mode", "opencv", "--gauss-mode", "opencv"]),
+        ("n4_640x480_scaledirect_fixed9", 640, 480, 15, ["--scaling", "direct", "--gauss-mode", "fixed9"]),
+        ("n4_640x480_scaledirect_fixed15", 640, 480, 16, ["--scaling", "direct", "--gauss-mode", "fixed15"])]
 
 
 @pytest.mark.skipif(not os.path.exists(REF_DRIVER), reason="oracle/_ref/ref_driver not built")

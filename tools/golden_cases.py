@@ -58,6 +58,7 @@ CASES = {
     "g256_scaledirect": ("g256",   ["--scaling", "direct"], False),
     "g64_scaledirect_rel": ("g64", ["--scaling", "direct", "--gauss-mode", "relative"], True),
     "g256_relative":    ("g256",   ["--gauss-mode", "relative"], False),
+    "g64_scaledirect_fixed9": ("g64", ["--scaling", "direct", "--gauss-mode", "fixed9"], True),
     "g64_fixed9":       ("g64",    ["--gauss-mode", "fixed9"], True),
     "g64_fixed15":      ("g64",    ["--gauss-mode", "fixed15"], True),
 }
