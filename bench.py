@@ -9,7 +9,8 @@ line on rank 0.  Workload = BASELINE.json configs[3]/[1] (1080p frames through e
 
   value     images/s over all GPUs, inputs already resident in HBM (psift_submit_dev_u8), results
             downloaded to pinned host memory (the download is part of the path).
-  e2e       the same through psift_submit_u8 with HOST buffers: private host copy + H2D inside.
+  e2e       the same with HOST buffers: page-locked input through psift_submit_pinned_u8 (H2D inside);
+            e2e.value_private_copy: pageable input through psift_submit_u8 (private pinned copy + H2D inside).
   roofline  pyramid stage (all k_blur2 launches of a frame): algorithmic bytes
             A_pyr = w*h + 4*L*sum(octave pixels) over the CUDA-event time of the stage.
   cpu_baseline  the CPU restatement (oracle/) timed on one host core on ONE frame -- the
@@ -198,6 +199,8 @@ def main():
     ctx = capi.Context(capi.default_config(), device=local)
     sub_dev = lambda t: ctx.submit_dev_u8(t.data_ptr(), W, H, W)
     sub_host = lambda im: ctx.submit(im)
+    pin_imgs = [torch.from_numpy(im).pin_memory() for im in imgs]          # the same frames in page-locked host memory
+    sub_pin = lambda t: ctx.submit_pinned_u8(t.data_ptr(), W, H, W)
 
     def timed(submit, src):
         """K steps: device time between two CUDA-event marks that join every stream of the context
@@ -221,8 +224,9 @@ def main():
         dt_dev, nf, nd, wall_dev = timed(sub_dev, dev_imgs)
     launches = (ctx.launch_count() - l0) * args.steps // (args.steps + args.warmup)
     b0 = ctx.d2h_bytes()
-    dt_e2e, nf2, nd2, wall_e2e = timed(sub_host, imgs)
+    dt_e2e, nf2, nd2, wall_e2e = timed(sub_pin, pin_imgs)
     d2h_per_step = (ctx.d2h_bytes() - b0) // (args.steps + args.warmup)
+    dt_copy, _, _, _ = timed(sub_host, imgs)          # psift_submit_u8: enqueue()'s semantics, pageable input + private copy
     n_frames = args.steps * BATCH
 
     # kernel-stage times (CUDA events on the frame's stream), one frame at a time, warm
@@ -272,6 +276,9 @@ def main():
                            "features_per_frame": nf / n_frames, "descriptors_per_frame": nd / n_frames},
                 "e2e": {"value": world * n_frames / dt_e2e, "unit": "images/s", "wall_value": world * n_frames / wall_e2e, "h2d_bytes_per_step": W * H * BATCH,
                         "d2h_bytes_per_step": int(d2h_per_step),
+                        "input": "page-locked host memory, psift_submit_pinned_u8 (uploaded straight from the caller's buffer)",
+                        "value_private_copy": world * n_frames / dt_copy,
+                        "private_copy_note": "psift_submit_u8 = PopSift::enqueue()'s contract: pageable caller buffer, copied into the library's pinned staging before the upload (the caller may free it at once)",
                         "d2h_note": "result bytes actually queued for download (each frame copies a prefix sized from earlier frames, +25 %%, so that no host round trip sits between the kernels and the download); the frames hold %d bytes of results per step" % int((nf2 * (52 + 44) + nd2 * 512) / args.steps)},
                 "gpu_launches": int(launches),
                 "stage_ms": stage,

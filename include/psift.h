@@ -119,6 +119,11 @@ void psift_destroy( psift_ctx* ctx );                               /* PopSift::
  * image therefore has to stay valid until psift_wait returns. */
 int  psift_submit_u8 ( psift_ctx* ctx, int w, int h, const uint8_t* host, size_t pitch_bytes, psift_job** out );
 int  psift_submit_f32( psift_ctx* ctx, int w, int h, const float*   host, size_t pitch_bytes, psift_job** out );
+/* same, but the image is in PAGE-LOCKED host memory (cudaHostAlloc / cudaHostRegister) that the caller leaves untouched
+ * until psift_wait returns: it is uploaded straight from there, without the private copy that psift_submit_u8 makes
+ * (SiftJob::SiftJob + Image::load copy twice, popsift.cpp:238-253, s_image.cu:71-79).  An extension: enqueue()'s
+ * "the caller may free its buffer at once" does not hold for this entry. */
+int  psift_submit_pinned_u8( psift_ctx* ctx, int w, int h, const uint8_t* pinned_host, size_t pitch_bytes, psift_job** out );
 /* same, input already resident in device memory (no H2D inside) */
 int  psift_submit_dev_u8( psift_ctx* ctx, int w, int h, const uint8_t* dev, size_t pitch_bytes, psift_job** out );
 int  psift_wait( psift_job* job, psift_result* out );               /* SiftJob::get, popsift.cpp:300-313 */

@@ -54,7 +54,7 @@ class DevInfo(C.Structure):
 
 
 EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "psift_create", "psift_configure",
-           "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_wait",
+           "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_submit_pinned_u8", "psift_wait",
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
            "psift_launch_count", "psift_d2h_bytes", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",
@@ -82,6 +82,7 @@ def lib():
         L.psift_submit_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
         L.psift_submit_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
         L.psift_submit_dev_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.psift_submit_pinned_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
         L.psift_wait.argtypes = [C.c_void_p, C.POINTER(Result)]
         L.psift_job_free.argtypes = [C.c_void_p]
         L.psift_octave_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -200,6 +201,12 @@ class Context:
             _chk(lib().psift_submit_f32(self._h, w, h, img.ctypes.data, w * 4, C.byref(job)))
         else:
             raise TypeError("image must be uint8 or float32")
+        return job
+
+    def submit_pinned_u8(self, ptr, w, h, pitch):
+        """image in page-locked host memory that stays untouched until wait(): uploaded without a private copy"""
+        job = C.c_void_p()
+        _chk(lib().psift_submit_pinned_u8(self._h, w, h, C.c_void_p(ptr), pitch, C.byref(job)))
         return job
 
     def submit_dev_u8(self, ptr, w, h, pitch):

@@ -650,6 +650,8 @@ void psift_destroy( psift_ctx* c )
     delete c;
 }
 
+static thread_local bool g_pinned_source = false;          /* set by psift_submit_pinned_u8 around submit_common */
+
 static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pitch, int elem, bool on_device, psift_job** out,
                           const Region& reg = Region() )
 {
@@ -716,9 +718,14 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
             CU( cudaMallocHost( &s.h_img, need ) );
             s.h_img_cap = need;
         }
-        if( pitch == s.img_pitch ) memcpy( s.h_img, src, pitch * ( h - 1 ) + row );
-        else for( int y = 0; y < h; y++ ) memcpy( (char*)s.h_img + y * s.img_pitch, (const char*)src + y * pitch, row );
-        CU( cudaMemcpyAsync( s.d_img, s.h_img, need, cudaMemcpyHostToDevice, s.stream ) );
+        if( g_pinned_source ) {
+            /* psift_submit_pinned_u8: the caller's buffer is page-locked and stays put until psift_wait: no private copy */
+            CU( cudaMemcpy2DAsync( s.d_img, s.img_pitch, src, pitch, row, h, cudaMemcpyHostToDevice, s.stream ) );
+        } else {
+            if( pitch == s.img_pitch ) memcpy( s.h_img, src, pitch * ( h - 1 ) + row );
+            else for( int y = 0; y < h; y++ ) memcpy( (char*)s.h_img + y * s.img_pitch, (const char*)src + y * pitch, row );
+            CU( cudaMemcpyAsync( s.d_img, s.h_img, need, cudaMemcpyHostToDevice, s.stream ) );
+        }
         rc = bind_input_texture( s, s.d_img, s.img_pitch, w, h, elem );
         if( rc ) return rc;
     }
@@ -735,6 +742,13 @@ int psift_submit_u8( psift_ctx* c, int w, int h, const uint8_t* host, size_t pit
 { return submit_common( c, w, h, host, pitch, 1, false, out ); }
 int psift_submit_f32( psift_ctx* c, int w, int h, const float* host, size_t pitch, psift_job** out )
 { return submit_common( c, w, h, host, pitch, 4, false, out ); }
+int psift_submit_pinned_u8( psift_ctx* c, int w, int h, const uint8_t* pinned_host, size_t pitch, psift_job** out )
+{
+    g_pinned_source = true;
+    const int rc = submit_common( c, w, h, pinned_host, pitch, 1, false, out );
+    g_pinned_source = false;
+    return rc;
+}
 int psift_submit_dev_u8( psift_ctx* c, int w, int h, const uint8_t* dev, size_t pitch, psift_job** out )
 { return submit_common( c, w, h, dev, pitch, 1, true, out ); }
 

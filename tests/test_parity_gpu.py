@@ -109,7 +109,11 @@ def test_device_resident_input_equals_host_input():
         a = ctx.extract(img)
         j = ctx.submit_dev_u8(t.data_ptr(), img.shape[1], img.shape[0], img.shape[1])
         b = ctx.wait(j); ctx.free(j)
+        p = torch.from_numpy(img).pin_memory()
+        j = ctx.submit_pinned_u8(p.data_ptr(), img.shape[1], img.shape[0], img.shape[1])
+        c = ctx.wait(j); ctx.free(j)
     assert a.feat.tobytes() == b.feat.tobytes() and a.desc.tobytes() == b.desc.tobytes()
+    assert a.feat.tobytes() == c.feat.tobytes() and a.desc.tobytes() == c.desc.tobytes()
 
 
 def test_reconfigure_and_resize():
