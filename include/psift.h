@@ -124,6 +124,10 @@ int  psift_submit_f32( psift_ctx* ctx, int w, int h, const float*   host, size_t
  * (SiftJob::SiftJob + Image::load copy twice, popsift.cpp:238-253, s_image.cu:71-79).  An extension: enqueue()'s
  * "the caller may free its buffer at once" does not hold for this entry. */
 int  psift_submit_pinned_u8( psift_ctx* ctx, int w, int h, const uint8_t* pinned_host, size_t pitch_bytes, psift_job** out );
+/* page-locked host memory for such images (cudaHostAlloc / cudaFreeHost behind the C ABI, for callers without a CUDA binding);
+ * fails without a CUDA device */
+int  psift_host_alloc_pinned( void** out, size_t bytes );
+void psift_host_free_pinned( void* p );
 /* same, input already resident in device memory (no H2D inside) */
 int  psift_submit_dev_u8( psift_ctx* ctx, int w, int h, const uint8_t* dev, size_t pitch_bytes, psift_job** out );
 int  psift_wait( psift_job* job, psift_result* out );               /* SiftJob::get, popsift.cpp:300-313 */

@@ -54,7 +54,7 @@ class DevInfo(C.Structure):
 
 
 EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "psift_create", "psift_configure",
-           "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_submit_pinned_u8", "psift_wait",
+           "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_submit_pinned_u8", "psift_host_alloc_pinned", "psift_host_free_pinned", "psift_wait",
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
            "psift_launch_count", "psift_d2h_bytes", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",

@@ -742,6 +742,18 @@ int psift_submit_u8( psift_ctx* c, int w, int h, const uint8_t* host, size_t pit
 { return submit_common( c, w, h, host, pitch, 1, false, out ); }
 int psift_submit_f32( psift_ctx* c, int w, int h, const float* host, size_t pitch, psift_job** out )
 { return submit_common( c, w, h, host, pitch, 4, false, out ); }
+int psift_host_alloc_pinned( void** out, size_t bytes )
+{
+    if( !out ) return fail( PSIFT_E_INVALID, "null argument" );
+    *out = nullptr;
+    int n = 0;
+    if( cudaGetDeviceCount( &n ) != cudaSuccess || n <= 0 ) { cudaGetLastError(); return fail( PSIFT_E_CUDA, "no CUDA device" ); }
+    const cudaError_t e = cudaHostAlloc( out, bytes ? bytes : 1, cudaHostAllocPortable );
+    if( e != cudaSuccess ) { cudaGetLastError(); *out = nullptr; return fail( PSIFT_E_CUDA, "cudaHostAlloc: %s", cudaGetErrorString( e ) ); }
+    return PSIFT_OK;
+}
+void psift_host_free_pinned( void* p ) { if( p ) cudaFreeHost( p ); }
+
 int psift_submit_pinned_u8( psift_ctx* c, int w, int h, const uint8_t* pinned_host, size_t pitch, psift_job** out )
 {
     g_pinned_source = true;
