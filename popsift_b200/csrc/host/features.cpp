@@ -2,6 +2,8 @@
 #include <popsift/features.h>
 #include <psift.h>
 #include <cstdio>
+#include <mutex>
+#include <iostream>
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -15,18 +17,52 @@ FeaturesBase::~FeaturesBase( ) { }
 
 FeaturesHost::FeaturesHost( ) : _ext( 0 ), _ori( 0 ) { }
 FeaturesHost::FeaturesHost( int num_ext, int num_ori ) : _ext( 0 ), _ori( 0 ) { reset( num_ext, num_ori ); }
-FeaturesHost::~FeaturesHost( ) { free( _ext ); free( _ori ); }
-
-static void* page_alloc( size_t bytes )
-{
-    void* p = 0;
-    if( posix_memalign( &p, (size_t)sysconf( _SC_PAGESIZE ), bytes ? bytes : 1 ) != 0 ) return 0;
-    return p;
+/* Page-aligned blocks (features.cu:58-82 uses posix_memalign) are recycled through a small process-wide cache: a
+ * fresh 1.5 MB block costs the worker thread ~400 page faults per frame, a recycled one none.  Blocks are handed out by
+ * size class (256 KB steps), at most 16 are kept, the cache is never torn down (results may outlive every PopSift). */
+namespace {
+struct BlockCache {
+    std::mutex mu;
+    struct E { size_t k; void* p; };
+    E e[16]; int n = 0;
+    static size_t klass( size_t b ) { const size_t g = 256 * 1024; return ( std::max<size_t>( b, 1 ) + g - 1 ) / g * g; }
+    void* get( size_t bytes )
+    {
+        const size_t k = klass( bytes );
+        {
+            std::lock_guard<std::mutex> lk( mu );
+            for( int i = 0; i < n; i++ ) if( e[i].k == k ) { void* p = e[i].p; e[i] = e[--n]; return p; }
+        }
+        void* p = 0;
+        if( posix_memalign( &p, (size_t)sysconf( _SC_PAGESIZE ), k ) != 0 ) return 0;
+        return p;
+    }
+    void put( void* p, size_t bytes )
+    {
+        if( !p ) return;
+        {
+            std::lock_guard<std::mutex> lk( mu );
+            if( n < 16 ) { e[n].k = klass( bytes ); e[n].p = p; n++; return; }
+        }
+        free( p );
+    }
+};
+BlockCache& block_cache() { static BlockCache* c = new BlockCache; return *c; }
 }
+
+FeaturesHost::~FeaturesHost( )
+{
+    block_cache().put( _ext, sizeof(Feature) * (size_t)getFeatureCount() );
+    block_cache().put( _ori, sizeof(Descriptor) * (size_t)getDescriptorCount() );
+}
+
+static void* page_alloc( size_t bytes ) { return block_cache().get( bytes ); }
+static void  page_free( void* p, size_t bytes ) { block_cache().put( p, bytes ); }
 
 void FeaturesHost::reset( int num_ext, int num_ori )
 {
-    free( _ext ); free( _ori ); _ext = 0; _ori = 0;
+    page_free( _ext, sizeof(Feature) * (size_t)getFeatureCount() ); page_free( _ori, sizeof(Descriptor) * (size_t)getDescriptorCount() );
+    _ext = 0; _ori = 0;
     _ext = (Feature*)page_alloc( sizeof(Feature) * (size_t)num_ext );
     _ori = (Descriptor*)page_alloc( sizeof(Descriptor) * (size_t)num_ori );
     if( !_ext || !_ori ) {

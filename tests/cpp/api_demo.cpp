@@ -17,6 +17,7 @@
 #include <string>
 #include <vector>
 #include <cmath>
+#include <chrono>
 #include <sstream>
 
 int main( int argc, char** argv )
@@ -52,6 +53,7 @@ int main( int argc, char** argv )
     PopSift sift( config, popsift::Config::ExtractingMode, PopSift::ByteImages );
 
     std::vector<SiftJob*> jobs;
+    const auto t_start = std::chrono::steady_clock::now();
     for( int i = 0; i < repeat; i++ ) jobs.push_back( sift.enqueue( w, h, img.data() ) );
     const std::vector<unsigned char> keep( img );
     std::fill( img.begin(), img.end(), 0 );          /* the job owns a private copy */
@@ -67,6 +69,8 @@ int main( int argc, char** argv )
         if( last ) delete last;
         last = feats;
     }
+    const double secs = std::chrono::duration<double>( std::chrono::steady_clock::now() - t_start ).count();
+    if( repeat > 1 ) fprintf( stderr, "%d frames through enqueue()/get() in %.3f s: %.1f frames/s\n", repeat, secs, repeat / secs );
     fprintf( stderr, "Number of feature points: %d, number of feature descriptors: %d, GPUs: %d\n",
              last->getFeatureCount(), last->getDescriptorCount(), sift.deviceCount() );
 
