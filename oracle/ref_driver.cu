@@ -190,6 +190,7 @@ int main( int argc, char** argv )
         else if( a == "--threshold" )    conf.setThreshold( (float)atof( next() ) );
         else if( a == "--edge-threshold" ) conf.setEdgeLimit( (float)atof( next() ) );
         else if( a == "--initial-blur" ) conf.setInitialBlur( (float)atof( next() ) );
+        else if( a == "--max-extrema" )  conf.setMaxExtrema( atoi( next() ) );
         else if( a == "--filter-max-extrema" ) conf.setFilterMaxExtrema( atoi( next() ) );
         else if( a == "--filter-grid" )  conf.setFilterGridSize( atoi( next() ) );
         else if( a == "--filter-sort" )  conf.setFilterSorting( std::string( next() ) );

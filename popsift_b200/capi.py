@@ -154,7 +154,7 @@ def config_from_flags(flags):
         key = f.lstrip("-").replace("-", "_")
         if key in ("mode", "gauss_mode", "desc_mode", "norm_mode", "filter_sort", "scaling"): kw[key] = v
         elif key == "downsampling": kw["downsampling"] = float(v)
-        elif key in ("octaves", "levels", "norm_multi", "filter_max_extrema"): kw[key] = int(v)
+        elif key in ("octaves", "levels", "norm_multi", "filter_max_extrema", "max_extrema"): kw[key] = int(v)
         elif key == "filter_grid": kw["filter_grid_size"] = int(v)
         elif key in ("sigma", "threshold", "initial_blur"): kw[key] = float(v)
         elif key == "edge_threshold": kw["edge_limit"] = float(v)

@@ -59,6 +59,19 @@ def gen(w, h, seed):
     return np.clip(np.rint(img), 0, 255).astype(np.uint8)
 
 
+def gen_tiled(w, h, seed, tile=2048):
+    """A giant image (config 5: 16384 x 16384) as a mosaic of independent gen() tiles: the same kind of content at a
+    cost linear in the area (gen() itself draws every blob in Python and holds two float coordinate planes)."""
+    img = np.empty((h, w), np.uint8)
+    k = 0
+    for y in range(0, h, tile):
+        for x in range(0, w, tile):
+            th, tw = min(tile, h - y), min(tile, w - x)
+            img[y:y + th, x:x + tw] = gen(tw, th, seed * 1000 + k)
+            k += 1
+    return img
+
+
 def constant(w, h, value=128):
     return np.full((h, w), value, dtype=np.uint8)
 

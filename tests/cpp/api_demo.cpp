@@ -24,7 +24,7 @@ int main( int argc, char** argv )
 {
     if( argc < 5 ) { fprintf( stderr, "usage: api_demo in.u8 w h out.bin [repeat] [flags]\n" ); return 2; }
     const int w = atoi( argv[2] ), h = atoi( argv[3] );
-    int repeat = 1, a = 5, tiled = 0;
+    int repeat = 1, a = 5, tiled = 0, as_float = 0;
     if( argc > 5 && argv[5][0] != '-' ) { repeat = atoi( argv[5] ); a = 6; }
 
     popsift::Config config;
@@ -37,12 +37,13 @@ int main( int argc, char** argv )
         else if( k == "--downsampling" ) config.setDownsampling( (float)atof( v.c_str() ) );
         else if( k == "--levels" ) config.setLevels( atoi( v.c_str() ) );
         else if( k == "--tiled" ) tiled = atoi( v.c_str() );
+        else if( k == "--float" ) as_float = atoi( v.c_str() );          /* in.u8 is a float32 file: PopSift::FloatImages */
         else if( k == "--log" ) config.setLogMode( v == "all" ? popsift::Config::All : popsift::Config::None );
         else if( k == "--mode" ) config.setMode( v == "vlfeat" ? popsift::Config::VLFeat : v == "opencv" ? popsift::Config::OpenCV : popsift::Config::PopSift );
         else { fprintf( stderr, "unknown flag %s\n", k.c_str() ); return 2; }
     }
 
-    std::vector<unsigned char> img( (size_t)w * h );
+    std::vector<unsigned char> img( (size_t)w * h * ( as_float ? sizeof(float) : 1 ) );
     FILE* f = fopen( argv[1], "rb" );
     if( !f || fread( img.data(), 1, img.size(), f ) != img.size() ) { fprintf( stderr, "cannot read %s\n", argv[1] ); return 2; }
     fclose( f );
@@ -50,11 +51,12 @@ int main( int argc, char** argv )
     popsift::cuda::device_prop_t deviceInfo;
     deviceInfo.set( 0, false );
 
-    PopSift sift( config, popsift::Config::ExtractingMode, PopSift::ByteImages );
+    PopSift sift( config, popsift::Config::ExtractingMode, as_float ? PopSift::FloatImages : PopSift::ByteImages );
 
     std::vector<SiftJob*> jobs;
     const auto t_start = std::chrono::steady_clock::now();
-    for( int i = 0; i < repeat; i++ ) jobs.push_back( sift.enqueue( w, h, img.data() ) );
+    for( int i = 0; i < repeat; i++ )
+        jobs.push_back( as_float ? sift.enqueue( w, h, reinterpret_cast<const float*>( img.data() ) ) : sift.enqueue( w, h, img.data() ) );
     const std::vector<unsigned char> keep( img );
     std::fill( img.begin(), img.end(), 0 );          /* the job owns a private copy */
 

@@ -8,7 +8,7 @@ from tools import golden_cases as gc
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(ROOT, "oracle", "cpu_sift")
-SKIP_FLAGS = {"relative"}   # Gauss mode not restated
+SKIP_FLAGS = {"relative", "--float-mode"}   # not restated: both are the texture unit's float blend
 CASES = [c for c, (_, flags, _) in gc.CASES.items()
          if os.path.exists(os.path.join(refio.GOLD, "ref", c + ".feat.bin")) and not (set(flags) & SKIP_FLAGS)]
 # bilinear float textures (igrid/notile) are blended in float on the CPU: descriptor tolerance is looser there

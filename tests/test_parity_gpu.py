@@ -31,13 +31,13 @@ def load(img):
 def test_features_match_reference_golden(case):
     img, flags, planes = gc.CASES[case]
     try:
-        cfg = capi.config_from_flags(flags)
+        cfg = capi.config_from_flags(gc.config_flags(flags))
         ctx = capi.Context(cfg)
     except capi.PsiftError as e:
         if "not built yet" in str(e): pytest.skip(str(e))
         raise
     with ctx:
-        mine = ctx.extract(load(img))
+        mine = ctx.extract(gc.float_image(img) if gc.is_float(flags) else load(img))     # float32 -> psift_submit_f32
         ref = refio.RefFeatures(os.path.join(refio.GOLD, "ref", case + ".feat.bin"))
         if "--filter-max-extrema" in flags and parity.filter_params(flags)[1] == "random":
             # which keypoints of a cell survive depends on the reference's atomic arrival order: only
@@ -140,21 +140,37 @@ def test_edge_inputs():
         capi.Context(capi.default_config(sigma=2.5))
 
 
-def test_float_image_path():
-    """float input in [0,1) (reference ImageFloat, s_image.cu:165-293): byte/255 as float gives the
-    same keypoint set as the byte image up to the sampler's conversion rounding."""
-    img = load("g256")
-    with capi.Context(capi.default_config()) as ctx:
-        a = ctx.extract(img)
-        b = ctx.extract((img.astype(np.float32) / np.float32(255.0)))
-    assert abs(a.n_feat - b.n_feat) <= max(2, a.n_feat // 20)
+def test_cpp_float_images_match_golden(tmp_path):
+    """PopSift(config, ExtractingMode, FloatImages) + enqueue(w, h, const float*) (reference popsift.h:73-167,
+    ImageFloat s_image.cu:175-293) against the reference's own float-image run (ref_driver --float-mode)."""
+    exe = os.path.join(ROOT, "tests", "cpp", "api_demo")
+    if not os.path.exists(exe): pytest.skip("tests/cpp/api_demo not built")
+    gold = os.path.join(refio.GOLD, "ref", "g256_float.feat.bin")
+    w, h, _ = gc.IMAGES["g256"]
+    src = tmp_path / "g256.f32"; gc.float_image("g256").tofile(src)
+    out = tmp_path / "api.bin"
+    r = subprocess.run([exe, str(src), str(w), str(h), str(out), "3", "--float", "1"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-800:]
+    b = out.read_bytes()
+    nf, nd = np.frombuffer(b, "<i4", 2)
+    feat = np.frombuffer(b, refio.FEATREC, nf, 8)
+    desc = np.frombuffer(b, "<f4", nd * 128, 8 + nf * refio.FEATREC.itemsize).reshape(nd, 128)
+    ref = refio.RefFeatures(gold)
+    assert (nf, nd) == (ref.n_feat, ref.n_desc)
+    key = lambda f: np.lexsort((f["x"], f["y"], f["octave"]))
+    a, c = feat[key(feat)], ref.feat[key(ref.feat)]
+    assert np.array_equal(a["x"], c["x"]) and np.array_equal(a["y"], c["y"]) and np.array_equal(a["sigma"], c["sigma"])
+    assert np.array_equal(a["num_ori"], c["num_ori"])
+    d = max(np.linalg.norm(desc[a["desc_idx"][i][k]] - ref.desc[c["desc_idx"][i][k]])
+            for i in range(nf) for k in range(a["num_ori"][i]) if c["desc_idx"][i][k] != ref.n_desc - 1)
+    assert d < parity.TOL_DESC
 
 
-def _run_ref(tmp_path, img, flags, name):
+def _run_ref(tmp_path, img, flags, name, timeout=300):
     p = tmp_path / (name + ".u8"); img.tofile(p)
     out = tmp_path / name
     r = subprocess.run([REF_DRIVER, "--in", str(p), "--w", str(img.shape[1]), "--h", str(img.shape[0]), "--out", str(out)] + flags,
-                       capture_output=True, text=True, timeout=300)
+                       capture_output=True, text=True, timeout=timeout)
     assert r.returncode == 0, r.stderr[-500:]
     return refio.RefFeatures(str(out) + ".feat.bin")
 
@@ -163,6 +179,17 @@ LIVE = [("c1_640x480_default", 640, 480, 1, []),
         ("c2_1080p_vlfeat_igrid", 1920, 1080, 2, ["--mode", "vlfeat", "--gauss-mode", "vlfeat", "--downsampling", "-1", "--desc-mode", "igrid"]),
         ("c4_1080p_default", 1920, 1080, 1000, []),
         ("c3_4k_opencv_rootsift", 3840, 2160, 3, ["--mode", "opencv", "--gauss-mode", "opencv", "--norm-mode", "RootSift"]),
+        # BASELINE.json configs[2] as stated: 4K, OpenCV mode, RootSift AND the max-feature cap (grid filter, s_filtergrid.cu:108-322)
+        ("c3_4k_opencv_rootsift_cap", 3840, 2160, 3, ["--mode", "opencv", "--gauss-mode", "opencv", "--norm-mode", "RootSift",
+                                                     "--filter-max-extrema", "4000", "--filter-grid", "4", "--filter-sort", "down"]),
+        ("c3_4k_down0_cap_up", 3840, 2160, 3, ["--mode", "opencv", "--gauss-mode", "opencv", "--downsampling", "0",
+                                              "--filter-max-extrema", "2500", "--filter-grid", "3", "--filter-sort", "up"]),
+        # the remaining descriptor modes at full size (s_desc_notile.cu, s_desc_grid.cu, s_desc_iloop.cu)
+        ("d_1080p_notile", 1920, 1080, 41, ["--desc-mode", "notile"]),
+        ("d_1080p_grid", 1920, 1080, 42, ["--desc-mode", "grid"]),
+        ("d_1080p_iloop", 1920, 1080, 43, ["--desc-mode", "iloop"]),
+        # float input at full size (ImageFloat, s_image.cu:175-293)
+        ("f_1080p_float", 1920, 1080, 44, ["--float-mode"]),
         # the remaining Gauss / scaling variants at a size where every octave count and span occurs
         ("n4_640x480_relative", 640, 480, 11, ["--gauss-mode", "relative"]),
         ("n4_640x480_scaledirect", 640, 480, 12, ["--scaling", "direct"]),
@@ -177,10 +204,33 @@ LIVE = [("c1_640x480_default", 640, 480, 1, []),
 def test_full_size_against_live_reference(tmp_path, name, w, h, seed, flags):
     """BASELINE.json configs at full size, reference CUDA build run side by side on the same bytes."""
     img = synth.gen(w, h, seed)
+    if gc.is_float(flags): img = img.astype(np.float32) / np.float32(255.0)
     ref = _run_ref(tmp_path, img, flags, name)
+    cfg = capi.config_from_flags(gc.config_flags(flags))
+    with capi.Context(cfg) as ctx:
+        mine = ctx.extract(img)
+    rep = parity.compare(mine, ref, norm_multi=cfg.norm_multi)
+    assert rep["ok_int"], rep
+    assert rep["xy_bitexact"] and rep["sigma_bitexact"], rep
+    if "grid" in flags:          # rounds sample positions: see LOOSE_DESC
+        assert rep["max_dtheta"] < parity.TOL_THETA and rep["max_desc_l2"] < 0.05, rep
+        return
+    assert rep["same_ori_diff_desc"] == 0, rep
+    assert rep["max_dtheta"] < parity.TOL_THETA and rep["max_desc_l2"] < parity.TOL_DESC, rep
+
+
+@pytest.mark.skipif(not os.path.exists(REF_DRIVER), reason="oracle/_ref/ref_driver not built")
+def test_config5_16384_against_live_reference(tmp_path):
+    """BASELINE.json configs[4] at its full size, un-tiled on one GPU on both sides (the reference has no tiled mode:
+    24 GB of arrays): 16384 x 16384, --downsampling 0, every keypoint and descriptor under the usual gates.
+    max_extrema is raised on both sides so that no octave is clamped (which keypoints a clamp keeps is arrival order)."""
+    img = synth.gen_tiled(16384, 16384, 5)
+    flags = ["--downsampling", "0", "--max-extrema", "400000"]
+    ref = _run_ref(tmp_path, img, flags, "c5_16384", timeout=900)
     cfg = capi.config_from_flags(flags)
     with capi.Context(cfg) as ctx:
         mine = ctx.extract(img)
+    assert ref.n_feat > 100000 and int(max(ref.ext_ct)) < 400000
     rep = parity.compare(mine, ref, norm_multi=cfg.norm_multi)
     assert rep["ok_int"], rep
     assert rep["xy_bitexact"] and rep["sigma_bitexact"], rep

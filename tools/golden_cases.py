@@ -61,7 +61,28 @@ CASES = {
     "g64_scaledirect_fixed9": ("g64", ["--scaling", "direct", "--gauss-mode", "fixed9"], True),
     "g64_fixed9":       ("g64",    ["--gauss-mode", "fixed9"], True),
     "g64_fixed15":      ("g64",    ["--gauss-mode", "fixed15"], True),
+    # float input images (reference ImageFloat, s_image.cu:175-293; PopSift::enqueue(int,int,const float*)): the
+    # same pictures as float32 u8/255, see float_image()
+    "g64_float":        ("g64",    ["--float-mode"], True),
+    "g256_float":       ("g256",   ["--float-mode"], False),
+    "g640_float":       ("g640",   ["--float-mode", "--downsampling", "0"], False),
 }
+VALUELESS = ("--float-mode",)
+
+
+def config_flags(flags):
+    """the flags that describe the Config (drops the ones that describe the input)"""
+    return [f for f in flags if f not in VALUELESS]
+
+
+def is_float(flags):
+    return "--float-mode" in flags
+
+
+def float_image(name):
+    """the float32 version of a golden input: u8 / 255 in float32, what both the reference run and the tests feed"""
+    w, h, _ = IMAGES[name]
+    return np.fromfile(image_path(name), np.uint8).reshape(h, w).astype(np.float32) / np.float32(255.0)
 
 
 # Matcher goldens (reference compute_distance, features.cu:184-225, run by `ref_driver --match-desc`): the left and

@@ -17,7 +17,11 @@ for case, (img, flags, planes) in gc.CASES.items():
     if only and case not in only:
         continue
     w, h, _ = gc.IMAGES[img]
-    cmd = [drv, "--in", gc.image_path(img), "--w", str(w), "--h", str(h), "--out", os.path.join(OUT, case)] + flags
+    src = gc.image_path(img)
+    if gc.is_float(flags):
+        src = os.path.join(OUT, "_" + img + ".f32")
+        gc.float_image(img).tofile(src)
+    cmd = [drv, "--in", src, "--w", str(w), "--h", str(h), "--out", os.path.join(OUT, case)] + flags
     if planes:
         cmd += ["--dump-planes", "--dump-tables"]
     try:
