@@ -39,7 +39,7 @@ static const char* USAGE =
 "Options:\n"
 "  -h [ --help ]            Print usage\n"
 "  -v [ --verbose ]\n"
-"  -l [ --log ]             Write debugging files (not available in this build)\n"
+"  -l [ --log ]             Write debugging files (the reference's dir-octave*/dir-dog*/dir-desc dumps)\n"
 "  -i [ --input-file ] arg  Input file (PGM/PPM) or directory\n"
 "Parameters:\n"
 "  --octaves arg  --levels arg  --sigma arg  --threshold arg  --edge-threshold arg  --edge-limit arg\n"

@@ -185,6 +185,9 @@ int  psift_last_timing( psift_ctx* ctx, float ms[8] );
  * it on only for the frames it measures the roofline on. */
 int  psift_debug_time_levels( psift_ctx* ctx, int on );
 int  psift_last_level_timing( psift_ctx* ctx, float* ms, int cap, int* n );
+/* frame slots of the context = the most jobs that can be in flight on it (6, or PSIFT_SLOTS); a submit beyond that
+ * returns PSIFT_E_STATE until a job has been waited for and freed */
+int psift_slot_count( psift_ctx* ctx );
 /* number of kernels this library launched since the context was created */
 long long psift_launch_count( psift_ctx* ctx );
 /* result bytes (counters, keypoint records, descriptors) queued for download to the host since the context was created */

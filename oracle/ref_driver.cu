@@ -37,6 +37,10 @@
 using namespace popsift;
 
 namespace popsift { __global__ void compute_distance( int3* match_matrix, Descriptor* l, int l_len, Descriptor* r, int r_len ); }
+/* The reference DECLARES Config::setMaxExtrema (sift_conf.h:114) but never defines it; this is the missing one-line
+ * definition, so that `--max-extrema` can lift the per-octave cap of 100 000 (sift_conf.cu:32) for the config-5 test
+ * (which keypoints a clamp keeps is atomic arrival order: no parity to speak of once an octave is clamped). */
+namespace popsift { void Config::setMaxExtrema( int extrema ) { _max_extrema = extrema; } }
 namespace popsift { __global__ void ori_par( const int octave, const int ext_ct_prefix_sum, cudaTextureObject_t layer, const int w, const int h ); }
 
 static void die( const char* msg ) { fprintf( stderr, "ref_driver: %s\n", msg ); exit( 2 ); }

@@ -57,7 +57,7 @@ EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "ps
            "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_submit_pinned_u8", "psift_host_alloc_pinned", "psift_host_free_pinned", "psift_wait",
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
-           "psift_launch_count", "psift_d2h_bytes", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",
+           "psift_launch_count", "psift_slot_count", "psift_d2h_bytes", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",
            "psift_extract_banded", "psift_banded_free", "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32",
            "psift_wait_dev", "psift_dev_features_alloc", "psift_dev_features_free", "psift_dev_features_info", "psift_match",
            "psift_match_dev", "psift_dev_download", "psift_dev_upload"]
@@ -76,6 +76,7 @@ def lib():
         L.psift_d2h_bytes.restype = C.c_longlong
         L.psift_d2h_bytes.argtypes = [C.c_void_p]
         L.psift_launch_count.argtypes = [C.c_void_p]
+        L.psift_slot_count.argtypes = [C.c_void_p]
         L.psift_create.argtypes = [C.c_int, C.POINTER(Config), C.POINTER(C.c_void_p)]
         L.psift_configure.argtypes = [C.c_void_p, C.POINTER(Config)]
         L.psift_destroy.argtypes = [C.c_void_p]

@@ -91,6 +91,7 @@ struct PopSiftImpl
     bool                    stop = false;
     bool                    started = false;
     std::atomic<long>       processed{ 0 };
+    int                     active = 0;                    /* jobs popped from the queue and not yet retired (under mu) */
     std::vector<psift_ctx*> ctx;
     std::vector<psift_ctx*> tiled_ctx;                     /* extractTiled()'s own contexts, band r on tiled_ctx[r] */
     psift_config            tiled_cfg;                     /* what they were last configured with */
@@ -99,7 +100,6 @@ struct PopSiftImpl
     psift_config            cfg;
     popsift::Config         conf;                          /* as configured (log mode, upscale factor for the debug dumps) */
     bool                    matching = false;              /* Config::MatchingMode: results stay on the device */
-    static const int        IN_FLIGHT = 6;              /* = the frame slots of a context */
 
     void worker( int idx );
     static FeaturesHost* convert( const psift_result& r );
@@ -128,22 +128,32 @@ void PopSiftImpl::worker( int idx )
 {
     psift_ctx* c = ctx[idx];
     std::deque<std::pair<SiftJob*, psift_job*> > inflight;
+    const int in_flight_max = std::max( 1, psift_slot_count( c ) );   /* the context's frame slots (PSIFT_SLOTS) */
+    SiftJob* held = 0;                                                /* popped, but the context had no free slot yet */
     for( ;; ) {
         /* fill the pipeline: block only when nothing is in flight */
-        while( (int)inflight.size() < IN_FLIGHT ) {
-            SiftJob* job = 0;
-            {
+        while( (int)inflight.size() < in_flight_max ) {
+            SiftJob* job = held;
+            held = 0;
+            if( !job ) {
                 std::unique_lock<std::mutex> lk( mu );
                 if( inflight.empty() ) cv.wait( lk, [&] { return stop || !queue.empty(); } );
-                if( !queue.empty() ) { job = queue.front(); queue.pop_front(); }
+                if( !queue.empty() ) { job = queue.front(); queue.pop_front(); active++; }
             }
             if( !job ) break;
             psift_job* pj = 0;
             int rc = job->data() == 0 ? PSIFT_E_INVALID
                    : job->isFloat() ? psift_submit_f32( c, job->width(), job->height(), (const float*)job->data(), 0, &pj )
                                     : psift_submit_u8 ( c, job->width(), job->height(), job->data(), 0, &pj );
+            if( rc == PSIFT_E_STATE && !inflight.empty() ) {
+                /* every slot is in flight (another user of the context, or fewer slots than expected): not a failure -
+                 * retire the oldest frame below and submit this job again */
+                held = job;
+                break;
+            }
             if( rc != PSIFT_OK ) {
                 std::cerr << "popsift: extraction failed: " << psift_last_error() << std::endl;
+                { std::lock_guard<std::mutex> lk( mu ); active--; }
                 job->setFeatures( matching ? (FeaturesBase*)new popsift::FeaturesDev( ) : (FeaturesBase*)new FeaturesHost( 0, 0 ) );
                 continue;
             }
@@ -170,7 +180,9 @@ void PopSiftImpl::worker( int idx )
         } else if( psift_wait( pj, &r ) == PSIFT_OK ) {
             fh = convert( r );
             if( r.n_desc == 0 && r.n_feat != 0 ) std::cerr << "Warning: no descriptors extracted" << std::endl;
-            if( conf.getLogMode() == popsift::Config::All )          /* popsift.cpp:201-209; the planes are still in the slot */
+            bool log_all;
+            { std::lock_guard<std::mutex> lk( mu ); log_all = conf.getLogMode() == popsift::Config::All; }
+            if( log_all )          /* popsift.cpp:201-209; the planes are still in the slot */
                 popsift::debug_dump_all( c, conf, r.n_octaves, r.n_levels, static_cast<FeaturesHost*>( fh ), "pyramid" );
         } else {
             std::cerr << "popsift: extraction failed: " << psift_last_error() << std::endl;
@@ -178,6 +190,7 @@ void PopSiftImpl::worker( int idx )
         }
         psift_job_free( pj );
         processed++;
+        { std::lock_guard<std::mutex> lk( mu ); active--; }
         job->setFeatures( fh );
     }
 }
@@ -205,10 +218,21 @@ bool PopSift::configure( const popsift::Config& config, bool force )
 {
     PopSiftImpl* I = _impl;
     if( I->processed.load() > 0 && !force ) return false;          /* popsift.cpp:65-67 */
-    _config = config;
-    _config.levels = std::max( 2, config.levels );                   /* popsift.cpp:71 */
-    _config.toC( &I->cfg );
-    I->conf = _config;
+    if( !I->ctx.empty() ) {
+        /* re-configuration: drain first (queued jobs AND jobs a worker has popped but not yet retired), so that no
+         * frame runs under a configuration other than the one it was enqueued with */
+        for( ;; ) {
+            { std::lock_guard<std::mutex> lk( I->mu ); if( I->queue.empty() && I->active == 0 ) break; }
+            std::this_thread::yield();
+        }
+    }
+    {
+        std::lock_guard<std::mutex> lk( I->mu );                     /* workers read conf (log mode) under the same lock */
+        _config = config;
+        _config.levels = std::max( 2, config.levels );               /* popsift.cpp:71 */
+        _config.toC( &I->cfg );
+        I->conf = _config;
+    }
     if( I->ctx.empty() ) {
         int n = psift_device_count();
         const char* env = getenv( "POPSIFT_NUM_GPUS" );
@@ -232,11 +256,6 @@ bool PopSift::configure( const popsift::Config& config, bool force )
         for( size_t k = 0; k < I->ctx.size(); k++ ) I->workers.emplace_back( &PopSiftImpl::worker, I, (int)k );
         I->started = true;
         return true;
-    }
-    /* re-configuration: drain first, contexts refuse while frames are in flight */
-    for( ;; ) {
-        { std::lock_guard<std::mutex> lk( I->mu ); if( I->queue.empty() ) break; }
-        std::this_thread::yield();
     }
     bool ok = true;
     for( auto c : I->ctx ) {
@@ -269,7 +288,11 @@ FeaturesHost* PopSift::extractTiled( int w, int h, const unsigned char* imageDat
     const int n_dev = (int)I->ctx.size();
     const int n = bands > 0 ? bands : n_dev;
     if( !I->tiled_ctx.empty() && memcmp( &I->tiled_cfg, &I->cfg, sizeof I->cfg ) != 0 )
-        for( auto c : I->tiled_ctx ) psift_configure( c, &I->cfg );   /* follow configure() */
+        for( auto c : I->tiled_ctx )                                  /* follow configure() */
+            if( psift_configure( c, &I->cfg ) != PSIFT_OK ) {
+                std::cerr << "popsift: tiled extraction: configure failed: " << psift_last_error() << std::endl;
+                return new FeaturesHost( 0, 0 );
+            }
     I->tiled_cfg = I->cfg;
     while( (int)I->tiled_ctx.size() < n ) {
         psift_ctx* c = 0;

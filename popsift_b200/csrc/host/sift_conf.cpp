@@ -1,10 +1,25 @@
 /* popsift::Config -- plain host code (reference src/popsift/sift_conf.cu; defaults :17-40,
  * string spellings :62-101, :131-141, :196-202; getPeakThreshold :275-278; equal :285-303). */
+#include <iostream>
+#include <cstdlib>
+#include <string>
 #include <popsift/sift_conf.h>
 #include <psift.h>
 #include <stdexcept>
 
 namespace popsift {
+
+/* A bad mode string: the reference prints the message and exits (POP_FATAL, sift_conf.cu:76,100,140,201).  Here the
+ * message goes to stderr too - so that a caller without a try block still sees why it died - and then
+ * std::invalid_argument is thrown; with POPSIFT_FATAL_EXIT=1 in the environment the process exits like the reference. */
+[[noreturn]] static void bad_mode( const std::string& msg )
+{
+    std::cerr << "popsift: " << msg << std::endl;
+    const char* e = getenv( "POPSIFT_FATAL_EXIT" );
+    if( e && atoi( e ) != 0 ) exit( -1 );
+    throw std::invalid_argument( msg );
+}
+
 
 Config::Config( )
     : octaves( -1 ), levels( 3 ), sigma( 1.6f ), _edge_limit( 10.0f )
@@ -34,7 +49,7 @@ void Config::setDescMode( const std::string& text )
     else if( text == "grid" )   setDescMode( Grid );
     else if( text == "igrid" )  setDescMode( IGrid );
     else if( text == "notile" ) setDescMode( NoTile );
-    else throw std::invalid_argument( "descriptor extraction mode must be one of loop, iloop, grid, igrid, notile" );
+    else bad_mode( "descriptor extraction mode must be one of loop, iloop, grid, igrid, notile" );
 }
 
 void Config::setGaussMode( const std::string& m )
@@ -46,7 +61,7 @@ void Config::setGaussMode( const std::string& m )
     else if( m == "opencv" )                 setGaussMode( OpenCV_Compute );
     else if( m == "fixed9" )                 setGaussMode( Fixed9 );
     else if( m == "fixed15" )                setGaussMode( Fixed15 );
-    else throw std::invalid_argument( std::string( "Bad Gauss mode. " ) + getGaussModeUsage() );
+    else bad_mode( std::string( "Bad Gauss mode. " ) + getGaussModeUsage() );
 }
 
 Config::GaussMode Config::getGaussModeDefault( ) { return VLFeat_Compute; }
@@ -64,7 +79,7 @@ void Config::setFilterSorting( const std::string& text )
     if( text == "up" )          _grid_filter_mode = SmallestScaleFirst;
     else if( text == "down" )   _grid_filter_mode = LargestScaleFirst;
     else if( text == "random" ) _grid_filter_mode = RandomScale;
-    else throw std::invalid_argument( "filter sorting mode must be one of up, down or random" );
+    else bad_mode( "filter sorting mode must be one of up, down or random" );
 }
 void Config::setFilterSorting( GridFilterMode m ) { _grid_filter_mode = m; }
 
@@ -73,7 +88,7 @@ void Config::setNormMode( const std::string& m )
 {
     if( m == "RootSift" )     setNormMode( RootSift );
     else if( m == "classic" ) setNormMode( Classic );
-    else throw std::invalid_argument( std::string( "Bad Normalization mode. " ) + getNormModeUsage() );
+    else bad_mode( std::string( "Bad Normalization mode. " ) + getNormModeUsage() );
 }
 void Config::setUseRootSift( bool on )         { _normalization_mode = on ? RootSift : Classic; }
 bool Config::getUseRootSift( ) const           { return _normalization_mode == RootSift; }

@@ -209,10 +209,10 @@ cudaError_t launch_grid_filter( const PyrLayout& L, const psift_config& cfg, Can
     int*   b_index   = reinterpret_cast<int*>( p );                     p += sizeof(int) * (size_t)ext_capacity;
     unsigned char* keep = reinterpret_cast<unsigned char*>( p );
     k_filter_plan<<<1, FG_NT, 0, st>>>( list, ct, plan, cfg.filter_grid_size, cfg.filter_max_extrema );
-    k_filter_bucket<<<148, 256, 0, st>>>( list, ct, L.n_oct, plan, b_scale, b_index );
-    k_filter_mark<<<148 * 4, 256, 0, st>>>( ct, plan, b_scale, b_index, keep, cfg.filter_sorting );
+    k_filter_bucket<<<sm_count(), 256, 0, st>>>( list, ct, L.n_oct, plan, b_scale, b_index );
+    k_filter_mark<<<sm_count() * 4, 256, 0, st>>>( ct, plan, b_scale, b_index, keep, cfg.filter_sorting );
     k_filter_compact<<<1, FG_NT, 0, st>>>( list, spare, ct, L.n_oct, plan, keep );
-    k_filter_copy<<<148, 256, 0, st>>>( spare, list, ct, plan );
+    k_filter_copy<<<sm_count(), 256, 0, st>>>( spare, list, ct, plan );
     if( launches ) *launches += 5;
     return cudaGetLastError();
 }

@@ -3,10 +3,11 @@
  * Reference: ori_par (s_orientation.cu:60-242) runs one 32-thread block per keypoint and
  * accumulates the 36-bin histogram with shared-memory float atomics, so its sums depend on
  * the arrival order; ori_prefix_sum (s_orientation.cu:303-345) is a single 32x32 block.
- * Here one WARP owns a keypoint (8 keypoints per block, grid-stride over a device-side
- * count: no host round trip), every lane accumulates a private histogram column in shared
- * memory in a fixed sample order and the columns are summed in lane order, which makes the
- * result reproducible run to run.  Sample geometry, weights, bin rounding, the 6 box-filter
+ * Here a 4-WARP BLOCK owns a keypoint (taken from a device-side work queue: no host round
+ * trip); the 128 threads stride over the window, every lane accumulates a private histogram
+ * column col[warp][bin][lane] in shared memory in a fixed sample order, the columns are
+ * summed in a fixed rotated lane order and the 4 warp partials in warp order, which makes
+ * the result reproducible run to run.  Sample geometry, weights, bin rounding, the 6 box-filter
  * passes, the parabola fit and the 0.8-of-best rule follow the reference expression by
  * expression (quirks kept: integer-truncated squared distance, s_orientation.cu:123; all
  * four slots filled with bin -1 when the histogram has no peak at all, :215-230).

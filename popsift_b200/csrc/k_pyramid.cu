@@ -36,6 +36,15 @@ bool pdl_enabled()
     return v != 0;
 }
 
+int sm_count()
+{
+    static int n[16] = { 0 };
+    int dev = 0; cudaGetDevice( &dev );
+    if( dev < 0 || dev >= 16 ) { int v = 148; cudaDeviceGetAttribute( &v, cudaDevAttrMultiProcessorCount, dev ); return v; }
+    if( !n[dev] ) { int v = 148; if( cudaDeviceGetAttribute( &v, cudaDevAttrMultiProcessorCount, dev ) != cudaSuccess ) { cudaGetLastError(); v = 148; } n[dev] = v; }
+    return n[dev];
+}
+
 constexpr int TX = 128;      /* tile width  (outputs) */
 constexpr int TY = 32;       /* tile height (outputs) */
 constexpr int VY = 8;        /* consecutive rows per thread in the vertical pass */

@@ -91,6 +91,7 @@ struct Slot {
 
 struct psift_ctx {
     int device = 0;
+    int n_sm = 148;                                         /* queried at create (grid sizes are multiples of it) */
     psift_config cfg;
     GaussTables  gt;
     Consts       K;
@@ -180,9 +181,20 @@ static int band_halo_rows( const psift_ctx* c, int split )
     return e + s_0 + 2;
 }
 
+static int setup_pyramid_impl( psift_ctx* c, Slot& s, int w, int h, const Region& reg );
 static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h, const Region& reg )
 {
+    const int rc = setup_pyramid_impl( c, s, w, h, reg );
+    /* a failure after the geometry was committed must not leave a slot that looks ready for this size */
+    if( rc != PSIFT_OK ) { s.in_w = s.in_h = 0; s.epoch++; }
+    return rc;
+}
+static int setup_pyramid_impl( psift_ctx* c, Slot& s, int w, int h, const Region& reg )
+{
     if( s.in_w == w && s.in_h == h && s.arena && s.reg_kind == reg.kind && s.reg_a == reg.y0 && s.reg_b == reg.y1 && s.reg_c == reg.split ) return PSIFT_OK;
+    /* everything that can be refused is refused before the slot's state is touched */
+    if( reg.kind == 1 && c->cfg.gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE )
+        return fail( PSIFT_E_INVALID, "the relative Gauss mode is not available for banded extraction" );
     int w0, h0;
     octave0_size( c->cfg, w, h, w0, h0 );
     const int n_oct = octave_count( c->cfg, w, h );
@@ -229,7 +241,6 @@ static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h, const Region& reg
         oh = (int)ceilf( oh / 2.0f );
     }
     const bool relative = c->cfg.gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE;
-    if( relative && reg.kind != 0 ) return fail( PSIFT_E_INVALID, "the relative Gauss mode is not available for banded extraction" );
     const size_t scratch_off = total;
     if( relative ) total += L.lstride[0];                                   /* horizontal-pass plane, octave-0 sized */
     if( total > s.arena_floats ) {
@@ -406,9 +417,9 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing )
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
     CU( stamp( s.ev[3] ) );
-    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, 148 * 10, st, &c->launches ) );
+    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, c->n_sm * 10, st, &c->launches ) );
     CU( stamp( s.ev[4] ) );
-    CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.lintex_d, c->d_dt, s.desc, s.feat, 148 * 4, st, &c->launches ) );
+    CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.lintex_d, c->d_dt, s.desc, s.feat, c->n_sm * 4, st, &c->launches ) );
     CU( stamp( s.ev[5] ) );
     CU( cudaMemcpyAsync( s.h_ct, s.ct, sizeof(Counters), cudaMemcpyDeviceToHost, st ) );
     if( s.pre_ext > 0 ) {
@@ -477,6 +488,8 @@ static int settle_frame( psift_ctx* c, Slot& s )
         if( rc ) return rc;
         CU( cudaEventSynchronize( s.ev_counters ) );
     }
+    if( s.h_ct->overflow )
+        return fail( PSIFT_E_STATE, "keypoint buffers still too small after 4 passes (%d keypoints, %d descriptors needed)", s.h_ct->need_ext, s.h_ct->need_desc );
     return PSIFT_OK;
 }
 
@@ -632,6 +645,7 @@ int psift_create( int device, const psift_config* cfg, psift_ctx** out )
     psift_ctx* c = new( std::nothrow ) psift_ctx;
     if( !c ) return fail( PSIFT_E_INVALID, "out of memory" );
     c->device = device;
+    if( cudaDeviceGetAttribute( &c->n_sm, cudaDevAttrMultiProcessorCount, device ) != cudaSuccess || c->n_sm < 1 ) { cudaGetLastError(); c->n_sm = 148; }
     int rc = psift_configure( c, cfg );
     if( rc ) { psift_destroy( c ); return rc; }
     *out = c;
@@ -658,6 +672,8 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
     if( !c || !out || !src ) return fail( PSIFT_E_INVALID, "null argument" );
     if( reg.kind != 0 && ( c->cfg.gauss_mode == PSIFT_GAUSS_FIXED9 || c->cfg.gauss_mode == PSIFT_GAUSS_FIXED15 ) )
         return fail( PSIFT_E_INVALID, "banded extraction is not available for the fixed9/fixed15 Gauss modes" );
+    if( reg.kind != 0 && c->cfg.scaling_mode == 1 )
+        return fail( PSIFT_E_INVALID, "banded extraction is not available with ScaleDirect scaling (every octave is filtered from the whole input image)" );
     if( reg.kind != 0 && c->cfg.filter_max_extrema > 0 ) return fail( PSIFT_E_INVALID, "the grid filter needs all keypoints of the image: not available for banded extraction" );
     *out = nullptr;
     if( w < 1 || h < 1 ) return fail( PSIFT_E_INVALID, "bad image size %dx%d", w, h );
@@ -963,6 +979,7 @@ int psift_last_level_timing( psift_ctx* c, float* ms, int cap, int* n )
     return PSIFT_OK;
 }
 
+int psift_slot_count( psift_ctx* c ) { return c ? (int)c->slots.size() : 0; }
 long long psift_launch_count( psift_ctx* c ) { return c ? c->launches : 0; }
 long long psift_d2h_bytes( psift_ctx* c ) { return c ? c->d2h_bytes : 0; }
 
