@@ -158,6 +158,16 @@ int  psift_dev_features_info( const psift_dev_features* f, psift_dev_info* info 
 int  psift_match( const psift_dev_features* l, const psift_dev_features* r, int* match3_host, float* dist2_host );
 int  psift_match_dev( int device, const float* l_desc_dev, int l_len, const float* r_desc_dev, int r_len,
                       int* match3_host, float* dist2_host );
+/* The matcher without any allocation, for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  It has no counterpart in the reference.
+ * Same arguments, same results as psift_match_dev; the device-side result scratch that psift_match_dev
+ * cudaMallocs per call is a static device array here (PSIFT_NOALLOC_MATCH_MAX x 20 bytes = 1.25 MiB, held by every GPU
+ * that loads the library until exit).  l_len > PSIFT_NOALLOC_MATCH_MAX returns PSIFT_E_INVALID with a message.  All calls
+ * on a GPU share the array (it keeps the last call's contents; the rows a call uses are cleared first): calls that
+ * overlap on the same GPU race - serialise them.  Calls no cudaMalloc / cudaFree / allocating routine. */
+#define PSIFT_NOALLOC_MATCH_MAX 65536
+int  psift_match_dev_noalloc( int device, const float* l_desc_dev, int l_len, const float* r_desc_dev, int r_len,
+                              int* match3_host, float* dist2_host );
 int  psift_dev_download( int device, const void* dev, void* host, size_t bytes );
 int  psift_dev_upload( int device, void* dev, const void* host, size_t bytes );
 

@@ -60,7 +60,7 @@ EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "ps
            "psift_launch_count", "psift_slot_count", "psift_d2h_bytes", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",
            "psift_extract_banded", "psift_banded_free", "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32",
            "psift_wait_dev", "psift_dev_features_alloc", "psift_dev_features_free", "psift_dev_features_info", "psift_match",
-           "psift_match_dev", "psift_dev_download", "psift_dev_upload"]
+           "psift_match_dev", "psift_match_dev_noalloc", "psift_dev_download", "psift_dev_upload"]
 
 _lib = None
 
@@ -110,6 +110,7 @@ def lib():
         L.psift_dev_features_info.argtypes = [C.c_void_p, C.POINTER(DevInfo)]
         L.psift_match.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.psift_match_dev.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.psift_match_dev_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.psift_dev_download.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
         L.psift_dev_upload.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
         L.psift_debug_mark_elapsed.argtypes = [C.c_void_p, C.POINTER(C.c_float)]

@@ -17,6 +17,8 @@
 #include "common.h"
 #include "kernels.h"
 #include <climits>
+#include <mutex>
+#include <cstdio>
 #include <math_constants.h>
 
 namespace psift {
@@ -167,3 +169,70 @@ cudaError_t launch_ref_features( const psift_feature* in, int n, float* desc_bas
 }
 
 } // namespace psift
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * psift_match_dev_noalloc: the matcher for callers that must not allocate (code under CUDA graph capture, serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * psift_match_dev keeps its device-side result buffers (int3 + float2 per left descriptor) in memory it
+ * cudaMallocs per call; here they live in ONE file-scope device array that every GPU which loads the library holds
+ * until exit: PSIFT_NOALLOC_MATCH_MAX left descriptors x 20 bytes = 1.25 MiB.
+ *   - the array's name is only a host-side stand-in in host code: its device address is taken once per device, with
+ *     that device current, through cudaGetSymbolAddress, and that pointer is what the kernel gets;
+ *   - all calls on a device share the array and it keeps the last call's contents: the rows a call uses are cleared
+ *     first, and two calls that overlap on the same GPU (two host threads) race - serialise them;
+ *   - nothing here calls cudaMalloc, cudaFree or any allocating routine.
+ * ------------------------------------------------------------------------------------------------------------- */
+namespace {
+constexpr size_t NA_MATCH_BYTES = (size_t)PSIFT_NOALLOC_MATCH_MAX * sizeof(int3);     /* 786 432: a multiple of 256 */
+constexpr size_t NA_TOTAL_BYTES = NA_MATCH_BYTES + (size_t)PSIFT_NOALLOC_MATCH_MAX * sizeof(float2);
+static_assert( NA_MATCH_BYTES % 256 == 0, "the float2 part must stay 256-byte aligned" );
+}
+static __device__ __align__( 256 ) unsigned char g_noalloc_match_scratch[NA_TOTAL_BYTES];
+
+namespace {
+constexpr int NA_MAX_DEV = 64;
+std::mutex     g_na_mu;
+unsigned char* g_na_ptr[NA_MAX_DEV] = { nullptr };
+
+/* device address of the scratch array on `device` (which must be current); looked up once per device */
+cudaError_t noalloc_scratch( int device, unsigned char** out )
+{
+    std::lock_guard<std::mutex> lk( g_na_mu );
+    if( device >= 0 && device < NA_MAX_DEV && g_na_ptr[device] ) { *out = g_na_ptr[device]; return cudaSuccess; }
+    unsigned char* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress( (void**)&p, g_noalloc_match_scratch );
+    if( e != cudaSuccess ) return e;
+    if( device >= 0 && device < NA_MAX_DEV ) g_na_ptr[device] = p;
+    *out = p;
+    return cudaSuccess;
+}
+}
+
+extern "C" int psift_match_dev_noalloc( int device, const float* l_desc_dev, int l_len, const float* r_desc_dev, int r_len,
+                                        int* match3_host, float* dist2_host )
+{
+    using psift::set_error;
+    if( l_len < 0 || r_len < 0 || ( l_len > 0 && ( !l_desc_dev || !match3_host ) ) || ( r_len > 0 && !r_desc_dev ) )
+        return set_error( PSIFT_E_INVALID, "psift_match_dev_noalloc: bad argument" );
+    if( l_len > PSIFT_NOALLOC_MATCH_MAX ) {
+        char msg[200];
+        snprintf( msg, sizeof msg, "psift_match_dev_noalloc: %d left descriptors exceed the static scratch (PSIFT_NOALLOC_MATCH_MAX = %d); use psift_match_dev",
+                  l_len, PSIFT_NOALLOC_MATCH_MAX );
+        return set_error( PSIFT_E_INVALID, msg );
+    }
+    if( l_len == 0 ) return PSIFT_OK;
+    cudaError_t e = cudaSetDevice( device );
+    unsigned char* base = nullptr;
+    if( e == cudaSuccess ) e = noalloc_scratch( device, &base );
+    if( e != cudaSuccess ) { cudaGetLastError(); return set_error( PSIFT_E_CUDA, cudaGetErrorString( e ) ); }
+    int*   d_m = reinterpret_cast<int*>( base );
+    float* d_d = reinterpret_cast<float*>( base + NA_MATCH_BYTES );
+    /* the array keeps the previous call's rows: clear what this call uses (the kernel writes every row it owns) */
+    e = cudaMemsetAsync( d_m, 0, sizeof(int3) * (size_t)l_len, 0 );
+    if( e == cudaSuccess ) e = cudaMemsetAsync( d_d, 0, sizeof(float2) * (size_t)l_len, 0 );
+    if( e == cudaSuccess ) e = psift::launch_match( l_desc_dev, l_len, r_desc_dev, r_len, d_m, d_d, 0 );
+    if( e == cudaSuccess ) e = cudaMemcpy( match3_host, d_m, sizeof(int) * 3 * (size_t)l_len, cudaMemcpyDeviceToHost );
+    if( e == cudaSuccess && dist2_host ) e = cudaMemcpy( dist2_host, d_d, sizeof(float) * 2 * (size_t)l_len, cudaMemcpyDeviceToHost );
+    if( e != cudaSuccess ) { cudaGetLastError(); return set_error( PSIFT_E_CUDA, cudaGetErrorString( e ) ); }
+    return PSIFT_OK;
+}

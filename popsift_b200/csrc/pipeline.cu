@@ -498,6 +498,7 @@ static int settle_frame( psift_ctx* c, Slot& s )
 /* ------------------------------------------------------------------------------------------ */
 
 namespace psift {
+int set_error( int code, const char* msg ) { return fail( code, "%s", msg ); }
 __global__ void k_dog_plane( const float* lo, const float* hi, float* out, int w, int h, int pitch )
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
