@@ -14,6 +14,7 @@
  */
 #include "common.h"
 #include "kernels.h"
+#include <cstdlib>
 
 namespace psift {
 
@@ -21,18 +22,33 @@ __device__ static const float PI_F  = 3.14159265358979323846f;          /* sift_
 __device__ static const float PI2_F = 2.0f * 3.14159265358979323846f;
 
 constexpr int ORI_WARPS = 4;
+constexpr int ORI_CH    = 1024;            /* samples per chunk: 32 steps of the reference's 32-thread loop */
 
+/* Histogram accumulation in the REFERENCE'S ORDER.  ori_par (s_orientation.cu:104-138) is one warp: sample i is taken by
+ * lane i % 32 in step i / 32 and added with a shared-memory float atomicAdd, which compiles to a compare-and-swap loop
+ * (ATOMS.CAST.SPIN in the SASS of the reference build): the lanes of a step that hit the same bin are added one after
+ * the other in lane order, the steps one after the other.  A float sum depends on its order, so the order is restated:
+ * every sample's (bin, weight) goes to shared memory together with its rank among the samples of its bin in that order
+ * (warp w takes a contiguous range of steps; __match_any_sync gives the lanes of a step that share a bin), the weights
+ * are scattered into per-bin lists, and thread b adds up list b front to back, continuing from hist[b].  Windows with
+ * more than ORI_CH samples take several chunks, in order.  Lane order within a step is ASCENDING: measured on B200
+ * against the reference build - 1 180 of 1 180 orientations of eight golden cases bit-equal (1 049 with descending order),
+ * and with them every descriptor. */
 __global__ void __launch_bounds__( ORI_WARPS * 32 )
 k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ cand, Counters* __restrict__ ct,
                psift_extremum* __restrict__ ext )
 {
-    __shared__ float col[ORI_WARPS][ORI_NBINS][32];     /* lane-private histogram columns */
+    __shared__ float          sw[ORI_CH];                /* weight of sample (chunk-local index) */
+    __shared__ float          lst[ORI_CH];               /* weights grouped by bin, in accumulation order */
+    __shared__ unsigned short sp[ORI_CH];                /* rank of the sample among its warp's samples of the same bin */
+    __shared__ unsigned char  sb[ORI_CH];                /* bin, or 63: outside the window's circle */
+    __shared__ int   wc[ORI_WARPS][ORI_NBINS];           /* samples per bin in warp w's range of steps */
+    __shared__ int   wbase[ORI_WARPS][ORI_NBINS];        /* where warp w's samples of bin b start in lst */
+    __shared__ int   bstart[ORI_NBINS + 1];
     __shared__ float hist[ORI_WARPS][ORI_NBINS];
     __shared__ float smh[ORI_WARPS][ORI_NBINS];
     __shared__ float yv[ORI_WARPS][64];
     __shared__ float ang[ORI_WARPS][64];
-
-    __shared__ float part[ORI_WARPS][ORI_NBINS];
     __shared__ int   next_e;
 
     pdl_enter();
@@ -40,10 +56,9 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
     const int lane = tid & 31;
     const int wid  = tid >> 5;
     const int total = ct->ext_total;
+    const unsigned lt_mask = ( 1u << lane ) - 1u;
 
-    /* a block per keypoint, handed out one at a time (windows differ in size by 5x and more): all
-     * eight warps share the window, each lane summing into its own histogram column, and the
-     * columns are added up in a fixed order - reproducible, unlike the reference's atomics */
+    /* a block per keypoint, handed out one at a time (windows differ in size by 5x and more) */
     for( ;; ) {
         if( tid == 0 ) next_e = atomicAdd( &ct->ori_next, 1 );
         __syncthreads();
@@ -55,9 +70,6 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
         const int  w = L.w[o], h = L.h[o];
         const float x = c.x, y = c.y, sig = c.sigma;
         const int   level = c.lpos;
-
-        #pragma unroll
-        for( int b = 0; b < ORI_NBINS; b++ ) col[wid][b][lane] = 0.0f;
 
         const float sigw   = __fmul_rn( 1.5f, sig );                       /* ORI_WINFACTOR */
         const int   rad    = (int)roundf( __fmul_rn( 3.0f, sigw ) );
@@ -73,46 +85,85 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
         const int pitch = L.pitch[o];
         const float* plane = L.base[o] + (size_t)min( max( level, 0 ), L.n_lvl - 1 ) * L.lstride[o];
         const int wxs = max( wx, 1 );
-        constexpr int NTH = ORI_WARPS * 32;
-        const int q = NTH / wxs, r = NTH - q * wxs;                         /* (row, column) advance per NTH pixels */
-        int yy = ymin + tid / wxs, xx = xmin + tid % wxs;
+        const int q32 = 32 / wxs, r32 = 32 - q32 * wxs;                     /* (row, column) advance per step */
 
-        for( int i = tid; i < loops; i += NTH ) {
-            /* 1 <= xx <= w-2 and 1 <= yy <= h-2: the four neighbours are inside the plane */
-            const float* p = plane + (size_t)yy * pitch + xx;
-            const float gx = __fsub_rn( __ldg( p + 1 ), __ldg( p - 1 ) );
-            const float gy = __fsub_rn( __ldg( p + pitch ), __ldg( p - pitch ) );
-            const float dx = __fsub_rn( (float)xx, x );
-            const float dy = __fsub_rn( (float)yy, y );
-            const int sq_dist = (int)__fmaf_rn( dy, dy, __fmul_rn( dx, dx ) );
-            if( sq_dist <= sq_thres ) {
-                const float grad  = hypotf( gx, gy );
-                const float theta = atan2f( gy, gx );
-                const float weight = __fmul_rn( grad, expf( __fmul_rn( (float)sq_dist, factor ) ) );
-                int bidx = (int)roundf( __fdividef( float( ORI_NBINS ) * ( theta + PI_F ), PI2_F ) );
-                bidx = ( bidx >= ORI_NBINS ) ? 0 : bidx;
-                col[wid][bidx][lane] += weight;
+        if( tid < ORI_NBINS ) hist[0][tid] = 0.0f;
+        for( int c0 = 0; c0 < loops; c0 += ORI_CH ) {
+            const int n_it = min( ORI_CH / 32, ( loops - c0 + 31 ) >> 5 );   /* steps in this chunk */
+            const int ipw  = ( n_it + ORI_WARPS - 1 ) / ORI_WARPS;          /* steps per warp: contiguous ranges */
+            const int it0  = wid * ipw, it1 = min( n_it, it0 + ipw );
+            for( int b = lane; b < ORI_NBINS; b += 32 ) wc[wid][b] = 0;
+            __syncwarp();
+            int i = c0 + 32 * it0 + lane;
+            int yy = ymin + i / wxs, xx = xmin + i % wxs;
+            for( int it = it0; it < it1; it++, i += 32 ) {
+                int key = 63; float weight = 0.0f;
+                if( i < loops ) {
+                    /* 1 <= xx <= w-2 and 1 <= yy <= h-2: the four neighbours are inside the plane */
+                    const float* p = plane + (size_t)yy * pitch + xx;
+                    const float gx = __fsub_rn( __ldg( p + 1 ), __ldg( p - 1 ) );
+                    const float gy = __fsub_rn( __ldg( p + pitch ), __ldg( p - pitch ) );
+                    const float dx = __fsub_rn( (float)xx, x );
+                    const float dy = __fsub_rn( (float)yy, y );
+                    const int sq_dist = (int)__fmaf_rn( dy, dy, __fmul_rn( dx, dx ) );
+                    if( sq_dist <= sq_thres ) {
+                        const float grad  = hypotf( gx, gy );
+                        const float theta = atan2f( gy, gx );
+                        weight = __fmul_rn( grad, expf( __fmul_rn( (float)sq_dist, factor ) ) );
+                        int bidx = (int)roundf( __fdividef( float( ORI_NBINS ) * ( theta + PI_F ), PI2_F ) );
+                        key = ( bidx >= ORI_NBINS ) ? 0 : bidx;
+                    }
+                }
+                const unsigned m = __match_any_sync( 0xffffffffu, key );
+                int before = 0;
+                if( key < ORI_NBINS ) before = wc[wid][key];
+                __syncwarp();
+                if( key < ORI_NBINS && ( m & lt_mask ) == 0 ) wc[wid][key] = before + __popc( m );
+                __syncwarp();
+                const int idx = 32 * it + lane;
+                sw[idx] = weight; sb[idx] = (unsigned char)key;
+                sp[idx] = (unsigned short)( before + __popc( m & lt_mask ) );
+                yy += q32; xx += r32; if( xx > xmax ) { xx -= wx; yy++; }
             }
-            yy += q; xx += r; if( xx > xmax ) { xx -= wx; yy++; }
-        }
-        __syncthreads();
-        for( int i = tid; i < ORI_WARPS * ORI_NBINS; i += NTH ) {
-            const int ww = i / ORI_NBINS, b = i - ww * ORI_NBINS;
-            float s = 0.0f;
-            #pragma unroll 8
-            for( int l = 0; l < 32; l++ ) s += col[ww][b][( l + b ) & 31];       /* rotated start: no bank conflict, still a fixed order */
-            part[ww][b] = s;
+            __syncthreads();
+            /* list layout: bins one after the other, within a bin warp 0's samples first */
+            if( wid == 0 ) {
+                int t0 = 0, t1 = 0;
+                #pragma unroll
+                for( int ww = 0; ww < ORI_WARPS; ww++ ) { t0 += wc[ww][lane]; if( lane < ORI_NBINS - 32 ) t1 += wc[ww][32 + lane]; }
+                int s0 = t0;
+                #pragma unroll
+                for( int d = 1; d < 32; d <<= 1 ) { const int v = __shfl_up_sync( 0xffffffffu, s0, d ); if( lane >= d ) s0 += v; }
+                const int all32 = __shfl_sync( 0xffffffffu, s0, 31 );
+                int s1 = t1;
+                #pragma unroll
+                for( int d = 1; d < 4; d <<= 1 ) { const int v = __shfl_up_sync( 0xffffffffu, s1, d ); if( lane >= d ) s1 += v; }
+                bstart[lane] = s0 - t0;
+                if( lane < ORI_NBINS - 32 ) bstart[32 + lane] = all32 + s1 - t1;
+                if( lane == ORI_NBINS - 32 - 1 ) bstart[ORI_NBINS] = all32 + s1;
+                __syncwarp();
+                for( int b = lane; b < ORI_NBINS; b += 32 ) {
+                    int run = bstart[b];
+                    #pragma unroll
+                    for( int ww = 0; ww < ORI_WARPS; ww++ ) { wbase[ww][b] = run; run += wc[ww][b]; }
+                }
+            }
+            __syncthreads();
+            for( int idx = tid; idx < 32 * n_it; idx += ORI_WARPS * 32 ) {
+                const int key = sb[idx];
+                if( key < ORI_NBINS ) lst[wbase[( idx >> 5 ) / ipw][key] + sp[idx]] = sw[idx];
+            }
+            __syncthreads();
+            if( tid < ORI_NBINS ) {
+                float acc = hist[0][tid];
+                const int j1 = bstart[tid + 1];
+                for( int j = bstart[tid]; j < j1; j++ ) acc = __fadd_rn( acc, lst[j] );
+                hist[0][tid] = acc;
+            }
+            __syncthreads();
         }
         __syncthreads();
         if( wid != 0 ) continue;            /* the rest is a warp's worth of work; the others wait at the next hand-out */
-        for( int b = lane; b < ORI_NBINS; b += 32 ) {
-            float s = 0.0f;
-            #pragma unroll
-            for( int ww = 0; ww < ORI_WARPS; ww++ ) s += part[ww][b];
-            hist[wid][b] = s;
-        }
-        __syncwarp();
-
         /* 3 x (two box passes), s_orientation.cu:143-160 */
         for( int it = 0; it < 3; it++ ) {
             for( int b = lane; b < ORI_NBINS; b += 32 ) {

@@ -59,8 +59,10 @@ def compare(mine, ref, norm_multi=0, skip_last_desc=True):
         ia = mf["desc_idx"][valid]; jr = rf["desc_idx"][valid]
         same_ori = (me["ori"].view(np.uint32) == re_["ori"].view(np.uint32))[valid]
         dth = dth_all[valid]
+        rep["ori_bitexact"] = (int(same_ori.sum()), int(valid.sum()))
     else:
         ia = jr = np.zeros(0, np.int64); same_ori = np.zeros(0, bool); dth = np.zeros(0, np.float32)
+        rep["ori_bitexact"] = (0, 0)
     keep = np.ones(len(ia), bool)
     if skip_last_desc and ref.n_desc % 32 != 0:
         keep = jr != ref.n_desc - 1        # reference race on its last descriptor (s_desc_normalize.h:21-32)

@@ -50,6 +50,10 @@ def test_features_match_reference_golden(case):
         assert rep["ok_int"], rep                      # counts, octave, level, num_ori: bit-exact
         assert rep["xy_bitexact"] and rep["sigma_bitexact"], rep
         assert rep["same_ori_diff_desc"] == 0, rep     # equal orientation => bit-equal descriptor
+        # the orientation histogram is accumulated in the reference's own order (k_orient.cu): every orientation of the
+        # golden cases is bit-equal to the reference's, and with it every descriptor of the modes that do not round
+        assert rep["ori_bitexact"][0] == rep["ori_bitexact"][1], rep
+        if case not in LOOSE_DESC: assert rep["desc_bitexact"][0] == rep["desc_bitexact"][1] or rep["max_desc_l2"] < 1e-6, rep
         assert rep["max_dtheta"] < parity.TOL_THETA, rep
         assert rep["max_desc_l2"] < LOOSE_DESC.get(case, parity.TOL_DESC), rep
         if planes:
