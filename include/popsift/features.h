@@ -45,8 +45,11 @@ class FeaturesHost : public FeaturesBase
 {
     Feature*    _ext;
     Descriptor* _ori;
+    void*       _block;   /* page-locked result block that _ori points into (handed over by the extraction), or 0 */
 public:
     FeaturesHost( );
+    /* descriptors already sit in `block` (a psift_result_block, psift.h): adopt it instead of copying */
+    FeaturesHost( int num_ext, int num_ori, Descriptor* descriptors_in_block, void* block );
     FeaturesHost( int num_ext, int num_ori );
     virtual ~FeaturesHost( );
 

@@ -30,7 +30,9 @@ class SiftJob
     int                 _h;
     unsigned char*      _imageData;     /* private copy, byte or float pixels */
     bool                _is_float;
+    bool                _pinned;        /* _imageData is a page-locked block of the library's recycled pool */
     popsift::ImageBase* _img;
+    void allocImage( size_t bytes, const void* src );
 public:
     /** byte image, value range 0..255 */
     SiftJob( int w, int h, const unsigned char* imageData );
@@ -52,6 +54,8 @@ public:
     int  height() const { return _h; }
     bool isFloat() const { return _is_float; }
     const unsigned char* data() const { return _imageData; }
+    bool isPinned() const { return _pinned; }
+    void releaseImage();               /* the upload is complete: the private copy goes back to the pool */
 };
 
 class PopSift
@@ -91,6 +95,7 @@ public:
     /* extensions */
     int  deviceCount() const;                 /* GPUs this object dispatches to */
     static void setDeviceLimit( int n );      /* use at most n GPUs (0 = all); call before constructing */
+    static void setDevices( int first, int count );   /* use GPUs first .. first+count-1 (count 0 = all from first); call before constructing */
     /* One giant image cut into row bands over all GPUs of this object (the reference runs such an
      * image un-tiled on one GPU): synchronous, returns the merged features, identical to the un-tiled result.  Uses its
      * own contexts (created on first use), so it may be called while enqueue()d jobs are in flight.  The caller owns

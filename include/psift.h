@@ -124,6 +124,7 @@ int  psift_submit_f32( psift_ctx* ctx, int w, int h, const float*   host, size_t
  * (SiftJob::SiftJob + Image::load copy twice, popsift.cpp:238-253, s_image.cu:71-79).  An extension: enqueue()'s
  * "the caller may free its buffer at once" does not hold for this entry. */
 int  psift_submit_pinned_u8( psift_ctx* ctx, int w, int h, const uint8_t* pinned_host, size_t pitch_bytes, psift_job** out );
+int  psift_submit_pinned_f32( psift_ctx* ctx, int w, int h, const float* pinned_host, size_t pitch_bytes, psift_job** out );   /* the same for float images */
 /* page-locked host memory for such images (cudaHostAlloc / cudaFreeHost behind the C ABI, for callers without a CUDA binding);
  * fails without a CUDA device */
 int  psift_host_alloc_pinned( void** out, size_t bytes );
@@ -131,6 +132,14 @@ void psift_host_free_pinned( void* p );
 /* same, input already resident in device memory (no H2D inside) */
 int  psift_submit_dev_u8( psift_ctx* ctx, int w, int h, const uint8_t* dev, size_t pitch_bytes, psift_job** out );
 int  psift_wait( psift_job* job, psift_result* out );               /* SiftJob::get, popsift.cpp:300-313 */
+/* psift_wait, and the caller TAKES the job's result buffers: out->feat / out->ext / out->desc stay valid after
+ * psift_job_free, until psift_result_block_free( *block ).  The block is page-locked memory from a process-wide pool of
+ * recycled blocks; the slot picks up another one for its next frame.  This is how PopSift's worker fills a FeaturesHost
+ * without copying the descriptors (the reference downloads straight into the FeaturesHost it returns, after a
+ * per-image cudaHostRegister: sift_pyramid.cu:281-321, features.cu:84-108). */
+typedef struct psift_result_block psift_result_block;
+int  psift_wait_take( psift_job* job, psift_result* out, psift_result_block** block );
+void psift_result_block_free( psift_result_block* block );
 void psift_job_free( psift_job* job );                              /* delete SiftJob */
 
 /* ---- Device-resident results and matching (reference Config::MatchingMode) ----------------------------------
@@ -195,6 +204,15 @@ int  psift_last_timing( psift_ctx* ctx, float ms[8] );
  * it on only for the frames it measures the roofline on. */
 int  psift_debug_time_levels( psift_ctx* ctx, int on );
 int  psift_last_level_timing( psift_ctx* ctx, float* ms, int cap, int* n );
+/* Measurement / test hook for the C++ classes (host/bench_shim.cpp): one PopSift object on GPUs first_device ..
+ * first_device + n_devices - 1 (n_devices 0: all from first_device), default Config; n_producers threads call
+ * PopSift::enqueue( w, h, frames[i % n_distinct] ) -- pageable caller memory -- and SiftJob::get(), each keeping at most
+ * `window` jobs outstanding; warm_frames untimed frames, then timed_frames frames between two wall-clock stamps
+ * (*seconds).  n_feat / n_desc / checksum are summed over the timed frames (positions and descriptor bytes are read). */
+int psift_cxx_stream( int first_device, int n_devices, int n_producers, int w, int h,
+                      const unsigned char* const* frames, int n_distinct, int warm_frames, int timed_frames,
+                      int window, double* seconds, long long* n_feat, long long* n_desc, double* checksum,
+                      int* devices_used );
 /* frame slots of the context = the most jobs that can be in flight on it (6, or PSIFT_SLOTS); a submit beyond that
  * returns PSIFT_E_STATE until a job has been waited for and freed */
 int psift_slot_count( psift_ctx* ctx );

@@ -54,10 +54,10 @@ class DevInfo(C.Structure):
 
 
 EXPORTS = ["psift_config_default", "psift_last_error", "psift_device_count", "psift_create", "psift_configure",
-           "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_submit_pinned_u8", "psift_host_alloc_pinned", "psift_host_free_pinned", "psift_wait",
+           "psift_destroy", "psift_submit_u8", "psift_submit_f32", "psift_submit_dev_u8", "psift_submit_pinned_u8", "psift_submit_pinned_f32", "psift_wait_take", "psift_result_block_free", "psift_host_alloc_pinned", "psift_host_free_pinned", "psift_wait",
            "psift_job_free", "psift_octave_size", "psift_debug_read_level", "psift_debug_read_dog",
            "psift_debug_gauss_table", "psift_debug_desc_tables", "psift_pyramid_geometry", "psift_last_timing",
-           "psift_launch_count", "psift_slot_count", "psift_d2h_bytes", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",
+           "psift_launch_count", "psift_slot_count", "psift_cxx_stream", "psift_d2h_bytes", "psift_debug_mark", "psift_debug_mark_elapsed", "psift_debug_time_levels", "psift_last_level_timing",
            "psift_extract_banded", "psift_banded_free", "psift_band_plan", "psift_submit_band_u8", "psift_band_seed", "psift_band_seed_copy", "psift_submit_seed_dev_f32",
            "psift_wait_dev", "psift_dev_features_alloc", "psift_dev_features_free", "psift_dev_features_info", "psift_match",
            "psift_match_dev", "psift_match_dev_noalloc", "psift_dev_download", "psift_dev_upload"]
@@ -77,6 +77,8 @@ def lib():
         L.psift_d2h_bytes.argtypes = [C.c_void_p]
         L.psift_launch_count.argtypes = [C.c_void_p]
         L.psift_slot_count.argtypes = [C.c_void_p]
+        L.psift_cxx_stream.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.psift_create.argtypes = [C.c_int, C.POINTER(Config), C.POINTER(C.c_void_p)]
         L.psift_configure.argtypes = [C.c_void_p, C.POINTER(Config)]
         L.psift_destroy.argtypes = [C.c_void_p]
@@ -85,6 +87,10 @@ def lib():
         L.psift_submit_dev_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
         L.psift_submit_pinned_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
         L.psift_wait.argtypes = [C.c_void_p, C.POINTER(Result)]
+        L.psift_wait_take.argtypes = [C.c_void_p, C.POINTER(Result), C.POINTER(C.c_void_p)]
+        L.psift_result_block_free.argtypes = [C.c_void_p]
+        L.psift_result_block_free.restype = None
+        L.psift_submit_pinned_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
         L.psift_job_free.argtypes = [C.c_void_p]
         L.psift_octave_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.psift_debug_read_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
@@ -311,6 +317,18 @@ class Context:
 
     def d2h_bytes(self):
         return int(lib().psift_d2h_bytes(self._h))
+
+
+def cxx_stream(imgs, warm_frames, timed_frames, first_device=0, n_devices=1, n_producers=1, window=8):
+    """psift_cxx_stream: the frames through PopSift::enqueue()/SiftJob::get() (the C++ classes); returns a dict"""
+    imgs = [np.ascontiguousarray(im, np.uint8) for im in imgs]
+    h, w = imgs[0].shape
+    ptrs = (C.c_void_p * len(imgs))(*[im.ctypes.data for im in imgs])
+    sec, nf, nd, cs, dev = C.c_double(), C.c_longlong(), C.c_longlong(), C.c_double(), C.c_int()
+    _chk(lib().psift_cxx_stream(first_device, n_devices, n_producers, w, h, ptrs, len(imgs), warm_frames, timed_frames, window,
+                                C.byref(sec), C.byref(nf), C.byref(nd), C.byref(cs), C.byref(dev)))
+    return {"seconds": sec.value, "n_feat": nf.value, "n_desc": nd.value, "checksum": cs.value, "devices": dev.value,
+            "images_per_sec": timed_frames / sec.value if sec.value > 0 else 0.0}
 
 
 def gauss_table(cfg, which, level):

@@ -15,8 +15,8 @@ namespace popsift {
 FeaturesBase::FeaturesBase( ) : _num_ext( 0 ), _num_ori( 0 ) { }
 FeaturesBase::~FeaturesBase( ) { }
 
-FeaturesHost::FeaturesHost( ) : _ext( 0 ), _ori( 0 ) { }
-FeaturesHost::FeaturesHost( int num_ext, int num_ori ) : _ext( 0 ), _ori( 0 ) { reset( num_ext, num_ori ); }
+FeaturesHost::FeaturesHost( ) : _ext( 0 ), _ori( 0 ), _block( 0 ) { }
+FeaturesHost::FeaturesHost( int num_ext, int num_ori ) : _ext( 0 ), _ori( 0 ), _block( 0 ) { reset( num_ext, num_ori ); }
 /* Page-aligned blocks (features.cu:58-82 uses posix_memalign) are recycled through a small process-wide cache: a
  * fresh 1.5 MB block costs the worker thread ~400 page faults per frame, a recycled one none.  Blocks are handed out by
  * size class (256 KB steps), at most 16 are kept, the cache is never torn down (results may outlive every PopSift). */
@@ -53,7 +53,20 @@ BlockCache& block_cache() { static BlockCache* c = new BlockCache; return *c; }
 FeaturesHost::~FeaturesHost( )
 {
     block_cache().put( _ext, sizeof(Feature) * (size_t)getFeatureCount() );
-    block_cache().put( _ori, sizeof(Descriptor) * (size_t)getDescriptorCount() );
+    if( _block ) psift_result_block_free( (psift_result_block*)_block );
+    else         block_cache().put( _ori, sizeof(Descriptor) * (size_t)getDescriptorCount() );
+}
+
+FeaturesHost::FeaturesHost( int num_ext, int num_ori, Descriptor* descriptors_in_block, void* block )
+    : _ext( 0 ), _ori( descriptors_in_block ), _block( block )
+{
+    _ext = (Feature*)block_cache().get( sizeof(Feature) * (size_t)num_ext );
+    if( !_ext ) {
+        std::cerr << "popsift: failed to allocate memory for " << num_ext << " features" << std::endl;
+        num_ext = num_ori = 0;
+    }
+    setFeatureCount( num_ext );
+    setDescriptorCount( num_ori );
 }
 
 static void* page_alloc( size_t bytes ) { return block_cache().get( bytes ); }
@@ -61,7 +74,9 @@ static void  page_free( void* p, size_t bytes ) { block_cache().put( p, bytes );
 
 void FeaturesHost::reset( int num_ext, int num_ori )
 {
-    page_free( _ext, sizeof(Feature) * (size_t)getFeatureCount() ); page_free( _ori, sizeof(Descriptor) * (size_t)getDescriptorCount() );
+    page_free( _ext, sizeof(Feature) * (size_t)getFeatureCount() );
+    if( _block ) { psift_result_block_free( (psift_result_block*)_block ); _block = 0; }
+    else page_free( _ori, sizeof(Descriptor) * (size_t)getDescriptorCount() );
     _ext = 0; _ori = 0;
     _ext = (Feature*)page_alloc( sizeof(Feature) * (size_t)num_ext );
     _ori = (Descriptor*)page_alloc( sizeof(Descriptor) * (size_t)num_ori );

@@ -49,27 +49,69 @@ static unsigned char* job_alloc( size_t n )
     return (unsigned char*)malloc( n ? n : 1 );
 }
 
+/* Page-locked blocks for the jobs' private copies, RECYCLED: enqueue() copies the caller's image straight into one (the
+ * one copy its contract needs, SiftJob::SiftJob popsift.cpp:238-253), the worker uploads from it without a second,
+ * staging copy (psift_submit_pinned_u8), and the block returns to the pool as soon as the frame has been retired.  A block
+ * is page-locked once, when the pool grows; the pool holds at most POOL_BYTES in all, jobs beyond that (a caller that
+ * enqueues thousands of frames up front) get ordinary memory and the staging path.  Size classes of 2 MB. */
+namespace {
+struct PinnedPool {
+    static const size_t GRAIN = (size_t)2 << 20, POOL_BYTES = (size_t)768 << 20;
+    std::mutex mu;
+    struct E { size_t k; void* p; };
+    std::vector<E> idle;
+    size_t         total = 0;          /* bytes page-locked so far (idle + in use) */
+    static size_t klass( size_t n ) { return ( std::max<size_t>( n, 1 ) + GRAIN - 1 ) / GRAIN * GRAIN; }
+    void* get( size_t n )
+    {
+        const size_t k = klass( n );
+        {
+            std::lock_guard<std::mutex> lk( mu );
+            for( size_t i = 0; i < idle.size(); i++ ) if( idle[i].k == k ) { void* p = idle[i].p; idle[i] = idle.back(); idle.pop_back(); return p; }
+            if( total + k > POOL_BYTES ) return 0;
+            total += k;
+        }
+        void* p = 0;
+        if( psift_host_alloc_pinned( &p, k ) != PSIFT_OK ) { std::lock_guard<std::mutex> lk( mu ); total -= k; return 0; }
+        return p;
+    }
+    void put( void* p, size_t n ) { std::lock_guard<std::mutex> lk( mu ); idle.push_back( E{ klass( n ), p } ); }
+};
+PinnedPool& pinned_pool() { static PinnedPool* p = new PinnedPool; return *p; }     /* never torn down: jobs may outlive every PopSift */
+}
+
+void SiftJob::allocImage( size_t n, const void* src )
+{
+    _imageData = (unsigned char*)pinned_pool().get( n );
+    _pinned = _imageData != 0;
+    if( !_imageData ) _imageData = job_alloc( n );
+    if( _imageData ) memcpy( _imageData, src, n );
+    else std::cerr << "popsift: SiftJob: out of memory for a " << _w << "x" << _h << " image" << std::endl;
+}
+
+void SiftJob::releaseImage()
+{
+    if( !_imageData ) return;
+    const size_t n = (size_t)_w * _h * ( _is_float ? sizeof(float) : 1 );
+    if( _pinned ) pinned_pool().put( _imageData, n ); else free( _imageData );
+    _imageData = 0; _pinned = false;
+}
+
 SiftJob::SiftJob( int w, int h, const unsigned char* imageData )
-    : _w( w ), _h( h ), _imageData( 0 ), _is_float( false ), _img( 0 )
+    : _w( w ), _h( h ), _imageData( 0 ), _is_float( false ), _pinned( false ), _img( 0 )
 {
     _f = _p.get_future().share();
-    const size_t n = (size_t)w * h;
-    _imageData = job_alloc( n );
-    if( _imageData ) memcpy( _imageData, imageData, n );
-    else std::cerr << "popsift: SiftJob: out of memory for a " << w << "x" << h << " image" << std::endl;
+    allocImage( (size_t)w * h, imageData );
 }
 
 SiftJob::SiftJob( int w, int h, const float* imageData )
-    : _w( w ), _h( h ), _imageData( 0 ), _is_float( true ), _img( 0 )
+    : _w( w ), _h( h ), _imageData( 0 ), _is_float( true ), _pinned( false ), _img( 0 )
 {
     _f = _p.get_future().share();
-    const size_t n = (size_t)w * h * sizeof(float);
-    _imageData = job_alloc( n );
-    if( _imageData ) memcpy( _imageData, imageData, n );
-    else std::cerr << "popsift: SiftJob: out of memory for a " << w << "x" << h << " image" << std::endl;
+    allocImage( (size_t)w * h * sizeof(float), imageData );
 }
 
-SiftJob::~SiftJob( ) { free( _imageData ); }
+SiftJob::~SiftJob( ) { releaseImage(); }
 
 void SiftJob::setImg( popsift::ImageBase* img ) { _img = img; }
 popsift::ImageBase* SiftJob::getImg() { return _img; }
@@ -82,6 +124,7 @@ popsift::FeaturesDev* SiftJob::getDev() { return dynamic_cast<popsift::FeaturesD
 /* ------------------------------------------------------------------ PopSift */
 
 static std::atomic<int> g_device_limit( 0 );
+static std::atomic<int> g_device_first( 0 );
 
 struct PopSiftImpl
 {
@@ -91,6 +134,7 @@ struct PopSiftImpl
     bool                    stop = false;
     bool                    started = false;
     std::atomic<long>       processed{ 0 };
+    int                     first_device = 0;              /* GPUs first_device .. first_device + ctx.size() - 1 */
     int                     active = 0;                    /* jobs popped from the queue and not yet retired (under mu) */
     std::vector<psift_ctx*> ctx;
     std::vector<psift_ctx*> tiled_ctx;                     /* extractTiled()'s own contexts, band r on tiled_ctx[r] */
@@ -102,15 +146,18 @@ struct PopSiftImpl
     bool                    matching = false;              /* Config::MatchingMode: results stay on the device */
 
     void worker( int idx );
-    static FeaturesHost* convert( const psift_result& r );
+    static FeaturesHost* convert( const psift_result& r, psift_result_block* block = 0 );
 };
 
-FeaturesHost* PopSiftImpl::convert( const psift_result& r )
+/* psift results -> FeaturesHost.  With a result block (psift_wait_take) the descriptors stay where the GPU put them and
+ * the FeaturesHost owns the block; only the 72-byte Feature records (host pointers into that block) are written here. */
+FeaturesHost* PopSiftImpl::convert( const psift_result& r, psift_result_block* block )
 {
-    FeaturesHost* fh = new FeaturesHost( r.n_feat, r.n_desc );
+    FeaturesHost* fh = block ? new FeaturesHost( r.n_feat, r.n_desc, (popsift::Descriptor*)r.desc, block )
+                             : new FeaturesHost( r.n_feat, r.n_desc );
     if( fh->getFeatureCount() != r.n_feat ) return fh;
     popsift::Descriptor* dbase = fh->getDescriptors();
-    if( r.n_desc > 0 ) memcpy( dbase, r.desc, sizeof(popsift::Descriptor) * (size_t)r.n_desc );
+    if( !block && r.n_desc > 0 ) memcpy( dbase, r.desc, sizeof(popsift::Descriptor) * (size_t)r.n_desc );
     popsift::Feature* f = fh->getFeatures();
     for( int i = 0; i < r.n_feat; i++ ) {
         const psift_feature& s = r.feat[i];
@@ -143,8 +190,10 @@ void PopSiftImpl::worker( int idx )
             if( !job ) break;
             psift_job* pj = 0;
             int rc = job->data() == 0 ? PSIFT_E_INVALID
-                   : job->isFloat() ? psift_submit_f32( c, job->width(), job->height(), (const float*)job->data(), 0, &pj )
-                                    : psift_submit_u8 ( c, job->width(), job->height(), job->data(), 0, &pj );
+                   : job->isFloat() ? ( job->isPinned() ? psift_submit_pinned_f32( c, job->width(), job->height(), (const float*)job->data(), 0, &pj )
+                                                        : psift_submit_f32( c, job->width(), job->height(), (const float*)job->data(), 0, &pj ) )
+                                    : ( job->isPinned() ? psift_submit_pinned_u8( c, job->width(), job->height(), job->data(), 0, &pj )
+                                                        : psift_submit_u8 ( c, job->width(), job->height(), job->data(), 0, &pj ) );
             if( rc == PSIFT_E_STATE && !inflight.empty() ) {
                 /* every slot is in flight (another user of the context, or fewer slots than expected): not a failure -
                  * retire the oldest frame below and submit this job again */
@@ -168,6 +217,7 @@ void PopSiftImpl::worker( int idx )
         SiftJob* job = inflight.front().first; psift_job* pj = inflight.front().second;
         inflight.pop_front();
         psift_result r;
+        psift_result_block* rb = 0;
         FeaturesBase* fh;
         if( matching ) {
             /* matchPrepareLoop, popsift.cpp:215-236: clone on the device, nothing goes to the host */
@@ -177,8 +227,8 @@ void PopSiftImpl::worker( int idx )
                 std::cerr << "popsift: extraction failed: " << psift_last_error() << std::endl;
                 fh = new popsift::FeaturesDev( );
             }
-        } else if( psift_wait( pj, &r ) == PSIFT_OK ) {
-            fh = convert( r );
+        } else if( psift_wait_take( pj, &r, &rb ) == PSIFT_OK ) {
+            fh = convert( r, rb );
             if( r.n_desc == 0 && r.n_feat != 0 ) std::cerr << "Warning: no descriptors extracted" << std::endl;
             bool log_all;
             { std::lock_guard<std::mutex> lk( mu ); log_all = conf.getLogMode() == popsift::Config::All; }
@@ -189,6 +239,7 @@ void PopSiftImpl::worker( int idx )
             fh = new FeaturesHost( 0, 0 );
         }
         psift_job_free( pj );
+        job->releaseImage();                 /* uploaded long ago: the page-locked copy can serve the next enqueue() */
         processed++;
         { std::lock_guard<std::mutex> lk( mu ); active--; }
         job->setFeatures( fh );
@@ -196,6 +247,7 @@ void PopSiftImpl::worker( int idx )
 }
 
 void PopSift::setDeviceLimit( int n ) { g_device_limit = n; }
+void PopSift::setDevices( int first, int count ) { g_device_first = std::max( 0, first ); g_device_limit = count; }
 
 PopSift::PopSift( ImageMode imode )
     : _impl( new PopSiftImpl ), _last_init_w( 0 ), _last_init_h( 0 ), _image_mode( imode )
@@ -238,6 +290,9 @@ bool PopSift::configure( const popsift::Config& config, bool force )
         const char* env = getenv( "POPSIFT_NUM_GPUS" );
         int lim = g_device_limit.load();
         if( env && atoi( env ) > 0 ) lim = atoi( env );
+        const int first = std::min( g_device_first.load(), std::max( 0, n - 1 ) );
+        n -= first;
+        I->first_device = first;
         if( lim > 0 && lim < n ) n = lim;
         if( n <= 0 ) {
             std::cerr << "popsift: no CUDA device found (this library has no CPU path)" << std::endl;
@@ -245,7 +300,7 @@ bool PopSift::configure( const popsift::Config& config, bool force )
         }
         for( int d = 0; d < n; d++ ) {
             psift_ctx* c = 0;
-            if( psift_create( d, &I->cfg, &c ) != PSIFT_OK ) {
+            if( psift_create( first + d, &I->cfg, &c ) != PSIFT_OK ) {
                 std::cerr << "popsift: cannot create a context on device " << d << ": " << psift_last_error() << std::endl;
                 continue;
             }
@@ -286,6 +341,7 @@ FeaturesHost* PopSift::extractTiled( int w, int h, const unsigned char* imageDat
     if( !I->started || !imageData ) { std::cerr << "popsift: extractTiled on an uninitialised PopSift object" << std::endl; return new FeaturesHost( 0, 0 ); }
     std::lock_guard<std::mutex> lk( I->tiled_mu );
     const int n_dev = (int)I->ctx.size();
+    const int g_tiled_first = I->first_device;
     const int n = bands > 0 ? bands : n_dev;
     if( !I->tiled_ctx.empty() && memcmp( &I->tiled_cfg, &I->cfg, sizeof I->cfg ) != 0 )
         for( auto c : I->tiled_ctx )                                  /* follow configure() */
@@ -296,7 +352,7 @@ FeaturesHost* PopSift::extractTiled( int w, int h, const unsigned char* imageDat
     I->tiled_cfg = I->cfg;
     while( (int)I->tiled_ctx.size() < n ) {
         psift_ctx* c = 0;
-        if( psift_create( (int)I->tiled_ctx.size() % n_dev, &I->cfg, &c ) != PSIFT_OK ) {
+        if( psift_create( g_tiled_first + (int)I->tiled_ctx.size() % n_dev, &I->cfg, &c ) != PSIFT_OK ) {
             std::cerr << "popsift: cannot create a context for a band: " << psift_last_error() << std::endl;
             return new FeaturesHost( 0, 0 );
         }

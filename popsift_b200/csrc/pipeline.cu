@@ -366,22 +366,87 @@ static int init_slot( psift_ctx* c, Slot& s )
     return PSIFT_OK;
 }
 
+/* Host result buffers are page-locked BLOCKS (keypoint records + descriptors) that can leave the slot: psift_wait_take
+ * hands the block of a finished job to the caller (the C++ FeaturesHost keeps it: no copy of the descriptors), and the
+ * slot picks up another one from a process-wide pool of recycled blocks for its next frame.  The downloads into a block
+ * are plain stream copies queued behind the frame's graph, so a new block needs no re-capture. */
+struct psift_result_block { psift_extremum* ext; psift_feature* feat; float* desc; int ext_cap, desc_cap; };
+namespace {
+struct ResultPool {
+    std::mutex mu;
+    std::vector<psift_result_block*> idle;
+    psift_result_block* get( int n_ext, int n_desc )
+    {
+        {
+            std::lock_guard<std::mutex> lk( mu );
+            for( size_t i = 0; i < idle.size(); i++ )
+                if( idle[i]->ext_cap >= n_ext && idle[i]->desc_cap >= n_desc ) { psift_result_block* b = idle[i]; idle[i] = idle.back(); idle.pop_back(); return b; }
+        }
+        psift_result_block* b = new( std::nothrow ) psift_result_block();
+        if( !b ) return nullptr;
+        b->ext_cap  = std::max( 4096, n_ext + n_ext / 2 );
+        b->desc_cap = std::max( 8192, n_desc + n_desc / 2 );
+        /* portable: a block may come back from one GPU's context and serve another's */
+        if( cudaHostAlloc( &b->ext,  sizeof(psift_extremum) * (size_t)b->ext_cap, cudaHostAllocPortable ) != cudaSuccess ||
+            cudaHostAlloc( &b->feat, sizeof(psift_feature) * (size_t)b->ext_cap, cudaHostAllocPortable ) != cudaSuccess ||
+            cudaHostAlloc( &b->desc, sizeof(float) * 128 * (size_t)b->desc_cap, cudaHostAllocPortable ) != cudaSuccess ) {
+            cudaGetLastError();
+            destroy( b );
+            return nullptr;
+        }
+        return b;
+    }
+    static void destroy( psift_result_block* b )
+    {
+        if( !b ) return;
+        if( b->ext ) cudaFreeHost( b->ext );
+        if( b->feat ) cudaFreeHost( b->feat );
+        if( b->desc ) cudaFreeHost( b->desc );
+        delete b;
+    }
+    void put( psift_result_block* b )
+    {
+        if( !b ) return;
+        {
+            std::lock_guard<std::mutex> lk( mu );
+            if( idle.size() < 64 ) { idle.push_back( b ); return; }
+        }
+        destroy( b );
+    }
+};
+ResultPool& result_pool() { static ResultPool* p = new ResultPool; return *p; }    /* never torn down: results may outlive every context */
+} // namespace
+
+static psift_result_block* detach_block( Slot& s )
+{
+    if( !s.h_ext ) return nullptr;
+    psift_result_block* b = new psift_result_block();
+    b->ext = s.h_ext; b->feat = s.h_feat; b->desc = s.h_desc; b->ext_cap = s.h_ext_cap; b->desc_cap = s.h_desc_cap;
+    s.h_ext = nullptr; s.h_feat = nullptr; s.h_desc = nullptr; s.h_ext_cap = s.h_desc_cap = 0;
+    return b;
+}
+
 static int ensure_host_results( Slot& s, int n_ext, int n_desc )
 {
-    if( n_ext > s.h_ext_cap ) {
-        if( s.h_ext ) cudaFreeHost( s.h_ext );
-        if( s.h_feat ) cudaFreeHost( s.h_feat );
-        const int cap = std::max( 4096, n_ext + n_ext / 2 );
-        CU( cudaMallocHost( &s.h_ext, sizeof(psift_extremum) * (size_t)cap ) );
-        CU( cudaMallocHost( &s.h_feat, sizeof(psift_feature) * (size_t)cap ) );
-        s.h_ext_cap = cap; s.epoch++;
+    if( s.h_ext && n_ext <= s.h_ext_cap && n_desc <= s.h_desc_cap ) return PSIFT_OK;
+    result_pool().put( detach_block( s ) );
+    psift_result_block* b = result_pool().get( std::max( n_ext, s.pre_ext ), std::max( n_desc, s.pre_desc ) );
+    if( !b ) return fail( PSIFT_E_CUDA, "out of page-locked host memory for %d keypoints / %d descriptors", n_ext, n_desc );
+    s.h_ext = b->ext; s.h_feat = b->feat; s.h_desc = b->desc; s.h_ext_cap = b->ext_cap; s.h_desc_cap = b->desc_cap;
+    delete b;
+    return PSIFT_OK;
+}
+
+/* the frame's own download of its results: the first pre_ext keypoints and pre_desc descriptors, right behind the kernels */
+static int queue_result_copies( Slot& s )
+{
+    cudaStream_t st = s.stream;
+    if( s.pre_ext > 0 ) {
+        CU( cudaMemcpyAsync( s.h_feat, s.feat, sizeof(psift_feature)  * (size_t)s.pre_ext, cudaMemcpyDeviceToHost, st ) );
+        CU( cudaMemcpyAsync( s.h_ext,  s.ext,  sizeof(psift_extremum) * (size_t)s.pre_ext, cudaMemcpyDeviceToHost, st ) );
     }
-    if( n_desc > s.h_desc_cap ) {
-        if( s.h_desc ) cudaFreeHost( s.h_desc );
-        const int cap = std::max( 8192, n_desc + n_desc / 2 );
-        CU( cudaMallocHost( &s.h_desc, sizeof(float) * 128 * (size_t)cap ) );
-        s.h_desc_cap = cap; s.epoch++;
-    }
+    if( s.pre_desc > 0 )
+        CU( cudaMemcpyAsync( s.h_desc, s.desc, sizeof(float) * 128 * (size_t)s.pre_desc, cudaMemcpyDeviceToHost, st ) );
     return PSIFT_OK;
 }
 
@@ -422,12 +487,7 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing )
     CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.lintex_d, c->d_dt, s.desc, s.feat, c->n_sm * 4, st, &c->launches ) );
     CU( stamp( s.ev[5] ) );
     CU( cudaMemcpyAsync( s.h_ct, s.ct, sizeof(Counters), cudaMemcpyDeviceToHost, st ) );
-    if( s.pre_ext > 0 ) {
-        CU( cudaMemcpyAsync( s.h_feat, s.feat, sizeof(psift_feature)  * (size_t)s.pre_ext, cudaMemcpyDeviceToHost, st ) );
-        CU( cudaMemcpyAsync( s.h_ext,  s.ext,  sizeof(psift_extremum) * (size_t)s.pre_ext, cudaMemcpyDeviceToHost, st ) );
-    }
-    if( s.pre_desc > 0 )
-        CU( cudaMemcpyAsync( s.h_desc, s.desc, sizeof(float) * 128 * (size_t)s.pre_desc, cudaMemcpyDeviceToHost, st ) );
+    if( !capturing ) return queue_result_copies( s );        /* a graph leaves them to run_frame: their target may change */
     return PSIFT_OK;
 }
 
@@ -463,6 +523,8 @@ static int run_frame( psift_ctx* c, Slot& s )
     if( want_graph ) {
         CU( cudaGraphLaunch( s.graph, s.stream ) );
         c->launches += s.graph_launches;
+        const int rcq = queue_result_copies( s );
+        if( rcq ) return rcq;
     } else {
         const int rc = enqueue_frame( c, s, false );
         if( rc ) return rc;
@@ -730,7 +792,7 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
         }
         /* the pinned copy has the DEVICE pitch, so that the upload is one linear transfer and not a row-by-row 2-D copy */
         const size_t need = s.img_pitch * h;
-        if( need > s.h_img_cap ) {
+        if( !g_pinned_source && need > s.h_img_cap ) {
             if( s.h_img ) cudaFreeHost( s.h_img );
             CU( cudaMallocHost( &s.h_img, need ) );
             s.h_img_cap = need;
@@ -775,6 +837,13 @@ int psift_submit_pinned_u8( psift_ctx* c, int w, int h, const uint8_t* pinned_ho
 {
     g_pinned_source = true;
     const int rc = submit_common( c, w, h, pinned_host, pitch, 1, false, out );
+    g_pinned_source = false;
+    return rc;
+}
+int psift_submit_pinned_f32( psift_ctx* c, int w, int h, const float* pinned_host, size_t pitch, psift_job** out )
+{
+    g_pinned_source = true;
+    const int rc = submit_common( c, w, h, pinned_host, pitch, 4, false, out );
     g_pinned_source = false;
     return rc;
 }
@@ -900,12 +969,28 @@ int psift_wait( psift_job* j, psift_result* r )
         c->last_slot = j->slot;
     }
     memset( r, 0, sizeof *r );
+    if( !s.h_ext && ( s.h_ct->ext_total > 0 || s.h_ct->ori_total > 0 ) )
+        return fail( PSIFT_E_STATE, "the results of this job were taken (psift_wait_take)" );
     r->n_feat = s.h_ct->ext_total; r->n_desc = s.h_ct->ori_total;
     r->feat = s.h_feat; r->desc = s.h_desc; r->ext = s.h_ext;
     for( int o = 0; o < MAX_OCT; o++ ) { r->ext_ct[o] = s.h_ct->ext_ct[o]; r->ori_ct[o] = s.h_ct->ori_ct[o]; }
     r->n_octaves = s.L.n_oct; r->n_levels = s.L.n_lvl; r->w0 = s.L.w[0]; r->h0 = s.L.h[0];
     return PSIFT_OK;
 }
+
+int psift_wait_take( psift_job* j, psift_result* r, psift_result_block** block )
+{
+    if( !block ) return fail( PSIFT_E_INVALID, "null argument" );
+    *block = nullptr;
+    const int rc = psift_wait( j, r );
+    if( rc ) return rc;
+    Slot& s = j->ctx->slots[j->slot];
+    /* r's pointers now belong to the block; the slot takes another one from the pool for its next frame */
+    *block = detach_block( s );
+    return PSIFT_OK;
+}
+
+void psift_result_block_free( psift_result_block* b ) { result_pool().put( b ); }
 
 void psift_job_free( psift_job* j )
 {

@@ -265,6 +265,28 @@ def test_cpp_api_demo_matches_golden(tmp_path):
     assert d < parity.TOL_DESC
 
 
+def test_cxx_classes_stream_equals_c_abi():
+    """PopSift::enqueue()/SiftJob::get() driven by several producer threads (psift_cxx_stream: page-locked job copies
+    from the recycled pool, FeaturesHost adopting the result block): the same keypoints and descriptor bytes as the C ABI."""
+    imgs = [load("g640"), synth.gen(640, 480, 2), synth.gen(640, 480, 3)]
+    with capi.Context(capi.default_config()) as ctx:
+        outs = [ctx.extract(im) for im in imgs]
+    def check(r):
+        c = float(np.sum(r.feat["x"].astype(np.float64) + r.feat["y"].astype(np.float64)))
+        for i in range(r.n_feat):
+            for k in range(int(r.feat["num_ori"][i])):
+                d = r.desc[r.feat["desc_idx"][i][k]]
+                c += float(d[0]) + float(d[127])
+        return c
+    n = 30                                                     # frames i % 3, ten times each
+    want_f = sum(o.n_feat for o in outs) * (n // 3); want_d = sum(o.n_desc for o in outs) * (n // 3)
+    want_c = sum(check(o) for o in outs) * (n // 3)
+    for producers, window in ((1, 4), (3, 2), (2, 9)):
+        got = capi.cxx_stream(imgs, 6, n, n_devices=1, n_producers=producers, window=window)
+        assert (got["n_feat"], got["n_desc"]) == (want_f, want_d), got
+        assert abs(got["checksum"] - want_c) <= 1e-6 * abs(want_c), (got, want_c)
+
+
 def test_log_mode_all_dumps(tmp_path):
     """Config::LogMode::All through the C++ class: the reference's debug files (sift_octave.cu:110-187, sift_pyramid.cu:88-106)
     in its formats; the float dumps must hold exactly the planes of the reference's own run."""
