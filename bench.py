@@ -32,6 +32,8 @@ PROFILE_SRC = "profiles/r01f_ncu_blur_march.txt"
 N_PYR_LAUNCHES = 46
 PYR_DRAM_BYTES = 229e6         # dram read+write of the 46 pyramid launches of one frame, same capture
 REF_REPEATS = 3
+CXX_PRODUCERS = 2     # caller threads per GPU that enqueue() and get() in the C++-class leg
+CXX_WINDOW = 6        # jobs each of them keeps outstanding
 REF_MAX_FRAMES = 2000
 
 
@@ -254,6 +256,26 @@ def main():
     dt_copy, _, _, _ = timed(sub_host, imgs)          # psift_submit_u8: enqueue()'s semantics, pageable input + private copy
     n_frames = args.steps * BATCH
 
+    # END TO END through the reference's own API: the C++ classes, PopSift::enqueue(w, h, pageable pointer) / SiftJob::get()
+    # (psift_cxx_stream, host/bench_shim.cpp): one PopSift object on this rank's GPU, CXX_PRODUCERS caller threads, frames
+    # enqueued at the rate they retire.  Wall clock inside the library call (the classes expose no device events): it
+    # contains the job copy, upload, kernels, result download and the walk over the returned features.  Max over ranks.
+    torch.cuda.synchronize(); barrier()
+    cxx = capi.cxx_stream(imgs, args.warmup * BATCH, n_frames, first_device=local, n_devices=1, n_producers=CXX_PRODUCERS, window=CXX_WINDOW)
+    barrier()
+    dt_cxx = pdist.max_over_ranks(cxx["seconds"])
+    cxx_feat = pdist.sum_over_ranks(cxx["n_feat"]) / world; cxx_desc = pdist.sum_over_ranks(cxx["n_desc"]) / world
+    # ONE PopSift object over all N GPUs of the box (its in-process dispatcher: one worker per GPU, shared queue), driven
+    # from rank 0 while the other ranks wait
+    one_object = None
+    if world > 1:
+        if rank == 0:
+            r1 = capi.cxx_stream(imgs, args.warmup * BATCH * world, n_frames * world, first_device=0, n_devices=world,
+                                 n_producers=CXX_PRODUCERS * world, window=CXX_WINDOW)
+            one_object = {"value": r1["images_per_sec"], "unit": "images/s", "devices": r1["devices"], "producer_threads": CXX_PRODUCERS * world,
+                          "what": "one PopSift object dispatching to all GPUs of this process (rank 0; the other ranks idle), wall clock"}
+        barrier()
+
     # kernel-stage times (CUDA events on the frame's stream), one frame at a time, warm
     stage = {}
     for i in range(8):
@@ -324,9 +346,13 @@ def main():
                 "config_detail": {"in_flight": IN_FLIGHT,
                                   "timing": "CUDA events joining all of the context's streams around the K steps (max over ranks); wall clock of the same region in wall_ms_per_step; stage times from CUDA events on the frame's stream",
                                   "features_per_frame": nf / n_frames, "descriptors_per_frame": nd / n_frames},
-                "e2e": {"value": world * n_frames / dt_e2e, "unit": "images/s", "wall_value": world * n_frames / wall_e2e, "h2d_bytes_per_step": W * H * BATCH,
+                "e2e": {"value": world * n_frames / dt_cxx, "unit": "images/s", "h2d_bytes_per_step": W * H * BATCH,
                         "d2h_bytes_per_step": int(d2h_per_step),
-                        "input": "page-locked host memory, psift_submit_pinned_u8 (uploaded straight from the caller's buffer)",
+                        "api": "the reference's C++ API: PopSift::enqueue(w, h, const unsigned char*) from pageable caller memory (private copy inside, as its contract says) and SiftJob::get() -> FeaturesHost, %d caller threads per GPU, %d jobs outstanding each; wall clock inside psift_cxx_stream, max over ranks" % (CXX_PRODUCERS, CXX_WINDOW),
+                        "features_per_frame": cxx_feat / n_frames, "descriptors_per_frame": cxx_desc / n_frames,
+                        "one_object": one_object,
+                        "c_abi_pinned": {"value": world * n_frames / dt_e2e, "wall_value": world * n_frames / wall_e2e,
+                                         "input": "page-locked host memory, psift_submit_pinned_u8 (uploaded straight from the caller's buffer), device-event time"},
                         "value_private_copy": world * n_frames / dt_copy,
                         "private_copy_note": "psift_submit_u8 = PopSift::enqueue()'s contract: pageable caller buffer, copied into the library's pinned staging before the upload (the caller may free it at once)",
                         "d2h_note": "result bytes actually queued for download (each frame copies a prefix sized from earlier frames, +25 %%, so that no host round trip sits between the kernels and the download); the frames hold %d bytes of results per step" % int((nf2 * (52 + 44) + nd2 * 512) / args.steps)},
