@@ -250,6 +250,7 @@ typedef struct psift_banded_result {
     psift_feature*  feat;
     psift_extremum* ext;
     float*          desc;
+    int             halo_exchange;   /* 1: halos were exchanged per level between neighbouring bands; 0: every band recomputed its halo */
 } psift_banded_result;
 int  psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8_t* host_img, size_t pitch,
                            int max_seed_pixels, psift_banded_result* out );

@@ -44,7 +44,7 @@ FSORT = {"random": 0, "down": 1, "up": 2}   # reference sift_conf.cu:131-141 (up
 class BandedResult(C.Structure):
     """psift_banded_result (psift.h)"""
     _fields_ = [("n_feat", C.c_int), ("n_desc", C.c_int), ("split_octave", C.c_int),
-                ("feat", C.c_void_p), ("ext", C.c_void_p), ("desc", C.c_void_p)]
+                ("feat", C.c_void_p), ("ext", C.c_void_p), ("desc", C.c_void_p), ("halo_exchange", C.c_int)]
 
 
 class DevInfo(C.Structure):
@@ -353,7 +353,7 @@ def band_plan(cfg, w, h, parts, max_seed_pixels=0):
 class BandedExtraction:
     """Result of extract_banded: same fields as Extraction / banded.Merged (feat, ext, desc, n_feat, n_desc)."""
     def __init__(self, r):
-        self.n_feat, self.n_desc, self.split = r.n_feat, r.n_desc, r.split_octave
+        self.n_feat, self.n_desc, self.split, self.halo_exchange = r.n_feat, r.n_desc, r.split_octave, r.halo_exchange
         def arr(ptr, n, dt):
             if n == 0: return np.zeros(0, dt)
             return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), (n * dt.itemsize,)).view(dt).copy()

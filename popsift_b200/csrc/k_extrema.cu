@@ -16,6 +16,7 @@
  */
 #include "common.h"
 #include "kernels.h"
+#include <algorithm>
 
 namespace psift {
 
@@ -364,38 +365,97 @@ __global__ void k_extrema_finish( Counters* ct, int n_oct, int max_extrema, int 
     ct->need_ext = need;
 }
 
-/* Deterministic order: rank every candidate of an octave by its detection voxel
- * (level, y, x) and scatter it to ext_ps[o] + rank.  The reference's order is whatever its
- * atomics produced (its own regression test sorts the output, testOxfordDataset.sh.in:138-155).
- * Keys are unique, so this is a permutation.  O(n^2/P) but n is a few thousand per octave. */
-constexpr int RS_NT = 256;
-__global__ void __launch_bounds__( RS_NT )
-k_rank_sort( const Cand* cand, int cand_stride, const Counters* ct, int n_oct, Cand* sorted )
+/* Deterministic order: every candidate of an octave goes to ext_ps[o] + (its rank under the key (level, y, x) of its
+ * detection voxel).  The reference's order is whatever its atomics produced (its own regression test sorts the output,
+ * testOxfordDataset.sh.in:138-155).  Keys are unique, so this is a permutation.
+ * Linear in the number of candidates (a giant image has > 100 000 per octave): counting sort by bucket = (level, band of
+ * rows) - monotonic in the key -, then the exact rank inside the candidate's own bucket (a few dozen entries) by
+ * comparison.  The scatter into bucket order uses an atomic cursor, so the order INSIDE a bucket of the intermediate
+ * list is arbitrary; the rank step does not depend on it. */
+constexpr int SORT_NT = 256;
+__device__ __forceinline__ unsigned long long cand_key( const Cand& c ) { return ( (unsigned long long)c.key_hi << 32 ) | c.key_lo; }
+__device__ __forceinline__ int cand_bucket( const Cand& c, int yshift )
 {
-    __shared__ unsigned long long keys[RS_NT];
+    const int level = (int)( c.key_hi >> 24 );
+    const int y     = (int)( ( ( c.key_hi & 0xffffffu ) << 4 ) | ( c.key_lo >> 28 ) );
+    return min( level, MAX_LVL - 1 ) * SORT_NBY + min( y >> yshift, SORT_NBY - 1 );
+}
+
+__global__ void __launch_bounds__( SORT_NT )
+k_sort_count( const Cand* cand, int cand_stride, const Counters* ct, SortScratch* ss, const __grid_constant__ SortShifts sh )
+{
     pdl_enter();
-    const int o = blockIdx.y;
-    const int n = ct->ext_ct[o];
+    const int o = blockIdx.y, n = ct->ext_ct[o];
     const Cand* src = cand + (size_t)o * cand_stride;
-    for( int i0 = blockIdx.x * RS_NT; i0 < n; i0 += gridDim.x * RS_NT ) {
-        const int i = i0 + threadIdx.x;
-        unsigned long long mykey = 0;
-        if( i < n ) mykey = ( (unsigned long long)src[i].key_hi << 32 ) | src[i].key_lo;
-        int rank = 0;
-        for( int j0 = 0; j0 < n; j0 += RS_NT ) {
-            __syncthreads();
-            const int j = j0 + threadIdx.x;
-            keys[threadIdx.x] = ( j < n ) ? ( ( (unsigned long long)src[j].key_hi << 32 ) | src[j].key_lo ) : ~0ull;
-            __syncthreads();
-            const int m = min( RS_NT, n - j0 );
-            for( int q = 0; q < m; q++ ) rank += ( keys[q] < mykey ) ? 1 : 0;
-        }
-        if( i < n ) sorted[ct->ext_ps[o] + rank] = src[i];
+    for( int i = blockIdx.x * SORT_NT + threadIdx.x; i < n; i += gridDim.x * SORT_NT )
+        atomicAdd( &ss->start[o][cand_bucket( src[i], sh.y[o] )], 1 );
+}
+
+/* counts -> exclusive prefix, one block per octave */
+__global__ void __launch_bounds__( 1024 )
+k_sort_scan( const Counters* ct, SortScratch* ss )
+{
+    __shared__ int wsum[32];
+    pdl_enter();
+    const int o = blockIdx.x;
+    if( ct->ext_ct[o] == 0 ) return;
+    constexpr int PER = SORT_NB / 1024;
+    static_assert( SORT_NB % 1024 == 0, "buckets per octave: a multiple of the block size" );
+    int v[PER], tot = 0;
+    #pragma unroll
+    for( int k = 0; k < PER; k++ ) { v[k] = ss->start[o][threadIdx.x * PER + k]; tot += v[k]; }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int inc = tot;
+    #pragma unroll
+    for( int d = 1; d < 32; d <<= 1 ) { const int u = __shfl_up_sync( 0xffffffffu, inc, d ); if( lane >= d ) inc += u; }
+    if( lane == 31 ) wsum[wid] = inc;
+    __syncthreads();
+    if( wid == 0 ) {
+        int w = wsum[lane];
+        #pragma unroll
+        for( int d = 1; d < 32; d <<= 1 ) { const int u = __shfl_up_sync( 0xffffffffu, w, d ); if( lane >= d ) w += u; }
+        wsum[lane] = w;
+    }
+    __syncthreads();
+    int run = inc - tot + ( wid ? wsum[wid - 1] : 0 );
+    #pragma unroll
+    for( int k = 0; k < PER; k++ ) { ss->start[o][threadIdx.x * PER + k] = run; run += v[k]; }
+}
+
+__global__ void __launch_bounds__( SORT_NT )
+k_sort_scatter( const Cand* cand, int cand_stride, const Counters* ct, SortScratch* ss, const __grid_constant__ SortShifts sh, Cand* grouped )
+{
+    pdl_enter();
+    const int o = blockIdx.y, n = ct->ext_ct[o];
+    const Cand* src = cand + (size_t)o * cand_stride;
+    Cand* dst = grouped + ct->ext_ps[o];
+    for( int i = blockIdx.x * SORT_NT + threadIdx.x; i < n; i += gridDim.x * SORT_NT ) {
+        const Cand c = src[i];
+        const int b = cand_bucket( c, sh.y[o] );
+        dst[ss->start[o][b] + atomicAdd( &ss->fill[o][b], 1 )] = c;
     }
 }
 
-cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted,
-                            int ext_capacity, Counters* ct, cudaStream_t st, long long* launches )
+__global__ void __launch_bounds__( SORT_NT )
+k_sort_rank( const Cand* grouped, const Counters* ct, const SortScratch* ss, const __grid_constant__ SortShifts sh, Cand* sorted )
+{
+    pdl_enter();
+    const int o = blockIdx.y, n = ct->ext_ct[o];
+    const Cand* src = grouped + ct->ext_ps[o];
+    Cand* dst = sorted + ct->ext_ps[o];
+    for( int i = blockIdx.x * SORT_NT + threadIdx.x; i < n; i += gridDim.x * SORT_NT ) {
+        const Cand c = src[i];
+        const int b = cand_bucket( c, sh.y[o] );
+        const int lo = ss->start[o][b], hi = lo + ss->fill[o][b];
+        const unsigned long long k = cand_key( c );
+        int rank = 0;
+        for( int j = lo; j < hi; j++ ) rank += ( cand_key( src[j] ) < k ) ? 1 : 0;
+        dst[lo + rank] = c;
+    }
+}
+
+cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted, Cand* sort_tmp,
+                            int ext_capacity, Counters* ct, SortScratch* ss, cudaStream_t st, long long* launches )
 {
     ExtGrid G;
     int nb = 0;
@@ -426,8 +486,15 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     }
 #undef PSIFT_EXT_LAUNCH
     launch_pdl( k_extrema_finish, dim3( 1 ), dim3( 32 ), 0, st, ct, L.n_oct, K.max_extrema, ext_capacity );
-    launch_pdl( k_rank_sort, dim3( 8, L.n_oct ), dim3( RS_NT ), 0, st, cand, cand_stride, ct, L.n_oct, sorted );
-    if( launches ) *launches += 3;
+    /* order the candidates (ss was zeroed together with the counters at the start of the frame) */
+    SortShifts sh;
+    for( int o = 0; o < MAX_OCT; o++ ) { int q = 0; while( o < L.n_oct && ( ( L.h[o] - 1 ) >> q ) >= SORT_NBY ) q++; sh.y[o] = q; }
+    const int gx = std::max( 1, std::min( 4 * sm_count(), ( ext_capacity + SORT_NT - 1 ) / SORT_NT ) ) / std::max( 1, L.oct_end - L.oct_begin ) + 1;
+    launch_pdl( k_sort_count,   dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, ss, sh );
+    launch_pdl( k_sort_scan,    dim3( L.n_oct ),     dim3( 1024 ),    0, st, ct, ss );
+    launch_pdl( k_sort_scatter, dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, ss, sh, sort_tmp );
+    launch_pdl( k_sort_rank,    dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, sort_tmp, ct, ss, sh, sorted );
+    if( launches ) *launches += 6;
     return cudaGetLastError();
 }
 

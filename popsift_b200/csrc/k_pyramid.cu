@@ -56,7 +56,9 @@ struct BlurArgs {
     float*              dst;
     float*              ds_dst;   /* level 0 of the next octave, or nullptr */
     int   w, h, pitch;            /* h: height of the whole plane (normalised texture coordinates) */
-    int   y_lo, y_hi;             /* rows [y_lo, y_hi) are stored and computed here (the whole plane unless banded);
+    int   r_lo, r_hi;             /* rows [r_lo, r_hi) of the source may be read: taps beyond are clamped to them (the plane's
+                                     true border, or - inside a band - further than any tap reaches) */
+    int   y_lo, y_hi;             /* rows [y_lo, y_hi) are computed here (the whole plane unless banded; within [r_lo, r_hi));
                                      src/dst/ds_dst point at the plane's row 0 even when that row is not stored */
     int   ds_pitch;
     float shift;                  /* FROM_TEX: texel shift, s_pyramid_build.cu:110-114 */
@@ -93,7 +95,7 @@ k_blur_level( const __grid_constant__ BlurArgs a )
              * a different texel than "last octave pixel" when the input is downscaled.  y is
              * clamped to the octave: the reference's vertical pass clamps on its row buffer. */
             const int gx = tx0 - HALO + c;
-            const int gy = min( max( ty0 - HALO + r, a.y_lo ), a.y_hi - 1 );
+            const int gy = min( max( ty0 - HALO + r, a.r_lo ), a.r_hi - 1 );
             const float rx = __fdiv_rn( (float)gx + a.shift, fw );
             const float ry = __fdiv_rn( (float)gy + a.shift, fh );
             S[r * SW + c] = tex2D<float>( a.tex, rx, ry );
@@ -104,7 +106,7 @@ k_blur_level( const __grid_constant__ BlurArgs a )
             constexpr int SW4 = SW / 4;
             for( int i = tid; i < ( r_hi - r_lo ) * SW4; i += NT ) {
                 const int r = r_lo + i / SW4, c4 = i % SW4;
-                const int gy = min( max( ty0 - HALO + r, a.y_lo ), a.y_hi - 1 );
+                const int gy = min( max( ty0 - HALO + r, a.r_lo ), a.r_hi - 1 );
                 const float4 v = __ldg( reinterpret_cast<const float4*>( a.src + (size_t)gy * a.pitch + ( tx0 - HALO ) ) + c4 );
                 reinterpret_cast<float4*>( S + r * SW )[c4] = v;
             }
@@ -112,7 +114,7 @@ k_blur_level( const __grid_constant__ BlurArgs a )
             for( int i = tid; i < ( r_hi - r_lo ) * SW; i += NT ) {
                 const int r = r_lo + i / SW, c = i % SW;
                 const int gx = min( max( tx0 - HALO + c, 0 ), w - 1 );
-                const int gy = min( max( ty0 - HALO + r, a.y_lo ), a.y_hi - 1 );
+                const int gy = min( max( ty0 - HALO + r, a.r_lo ), a.r_hi - 1 );
                 S[r * SW + c] = __ldg( a.src + (size_t)gy * a.pitch + gx );
             }
         }
@@ -274,8 +276,8 @@ k_blur2( const __grid_constant__ BlurArgs a )
         #pragma unroll
         for( int k = 0; k < NC; k++ ) rx[k] = __fdiv_rn( (float)( tx0 - HX + lane + 32 * k ) + a.shift, fw );   /* x unclamped: see k_blur_level */
         for( int p = wid; p < RPn; p += NT / 32 ) {
-            const int g0 = min( max( ty0 - H + 2 * p, a.y_lo ), a.y_hi - 1 );
-            const int g1 = min( max( ty0 - H + 2 * p + 1, a.y_lo ), a.y_hi - 1 );
+            const int g0 = min( max( ty0 - H + 2 * p, a.r_lo ), a.r_hi - 1 );
+            const int g1 = min( max( ty0 - H + 2 * p + 1, a.r_lo ), a.r_hi - 1 );
             const float ry0 = __fdiv_rn( (float)g0 + a.shift, fh ), ry1 = __fdiv_rn( (float)g1 + a.shift, fh );
             #pragma unroll
             for( int k = 0; k < NC; k++ ) {
@@ -293,8 +295,8 @@ k_blur2( const __grid_constant__ BlurArgs a )
             for( int u = 0; u < 4; u++ ) {
                 const int i = min( i0 + u * NT, RPn * SW - 1 );
                 const int p = i / SW, c = i % SW;
-                const int g0 = min( max( ty0 - H + 2 * p, a.y_lo ), a.y_hi - 1 );
-                const int g1 = min( max( ty0 - H + 2 * p + 1, a.y_lo ), a.y_hi - 1 );
+                const int g0 = min( max( ty0 - H + 2 * p, a.r_lo ), a.r_hi - 1 );
+                const int g1 = min( max( ty0 - H + 2 * p + 1, a.r_lo ), a.r_hi - 1 );
                 const int gx = min( max( tx0 - HX + c, 0 ), w - 1 );
                 v[u] = make_float2( __ldg( a.src + (size_t)g0 * a.pitch + gx ), __ldg( a.src + (size_t)g1 * a.pitch + gx ) );
             }
@@ -310,8 +312,8 @@ k_blur2( const __grid_constant__ BlurArgs a )
         #pragma unroll T::UNR
         for( int i = tid; i < RPn * SQ; i += NT ) {
             const int p = i / SQ, c4 = i % SQ;
-            const int g0 = min( max( ty0 - H + 2 * p, a.y_lo ), a.y_hi - 1 );
-            const int g1 = min( max( ty0 - H + 2 * p + 1, a.y_lo ), a.y_hi - 1 );
+            const int g0 = min( max( ty0 - H + 2 * p, a.r_lo ), a.r_hi - 1 );
+            const int g1 = min( max( ty0 - H + 2 * p + 1, a.r_lo ), a.r_hi - 1 );
             const float4 A = __ldg( reinterpret_cast<const float4*>( a.src + (size_t)g0 * a.pitch + ( tx0 - HX ) ) + c4 );
             const float4 B = __ldg( reinterpret_cast<const float4*>( a.src + (size_t)g1 * a.pitch + ( tx0 - HX ) ) + c4 );
             S4[p * 2 * SQ + c4]      = make_float4( A.x, B.x, A.y, B.y );
@@ -503,7 +505,7 @@ k_blur_march( const __grid_constant__ MarchArgs m )
     auto request = [&]( int q ) {
         float* sb = reinterpret_cast<float*>( S4 + ( q % NB ) * SBUF ) + sbase;
         const int row_first = r0 - H + q * RS;
-        if( !FROM_TEX && !edge && row_first >= a.y_lo && row_first + RS <= a.y_hi ) {
+        if( !FROM_TEX && !edge && row_first >= a.r_lo && row_first + RS <= a.r_hi ) {
             /* the common step: no clamping anywhere, one row pointer and constant offsets */
             const float* gr = a.src + (long long)( row_first + hp ) * a.pitch + gx0;
             #pragma unroll
@@ -518,7 +520,7 @@ k_blur_march( const __grid_constant__ MarchArgs m )
         }
         #pragma unroll
         for( int rp = 0; rp < NRP; rp++ ) {
-            const int g = min( max( r0 - H + q * RS + 2 * rp + hp, a.y_lo ), a.y_hi - 1 );
+            const int g = min( max( r0 - H + q * RS + 2 * rp + hp, a.r_lo ), a.r_hi - 1 );
             if( FROM_TEX ) {
                 const float ry = __fdiv_rn( (float)g + a.shift, (float)a.h );
                 #pragma unroll
@@ -1018,7 +1020,7 @@ static cudaError_t launch_pyramid_fixed( const PyrLayout& L, cudaTextureObject_t
             /* ScaleDirect with the fixed modes (s_pyramid_build.cu:478-486): level 0 of the octave comes from the input image
              * (horizontal dd[o], vertical inc[0]) instead of the previous octave; the levels above it as usual */
             BlurArgs b;
-            b.w = L.w[o]; b.h = L.h[o]; b.pitch = L.pitch[o]; b.y_lo = L.row_lo[o]; b.y_hi = L.row_hi[o];
+            b.w = L.w[o]; b.h = L.h[o]; b.pitch = L.pitch[o]; b.y_lo = L.cmp_lo[o]; b.y_hi = L.cmp_hi[o]; b.r_lo = L.row_lo[o]; b.r_hi = L.row_hi[o];
             b.dst = L.base[o]; b.ds_dst = nullptr; b.ds_pitch = 0; b.shift = 0.5f;
             b.src = nullptr; b.tex = input_tex; b.th = T.dd[o]; b.tv = T.inc[0];
             cudaError_t e = launch_blur<true>( b, st );
@@ -1043,6 +1045,44 @@ static cudaError_t launch_pyramid_fixed( const PyrLayout& L, cudaTextureObject_t
         }
     }
     return cudaSuccess;
+}
+
+/* one Gaussian level of one octave (default Gauss modes: vlfeat, opencv, vlfeat-direct), onto stream st */
+static cudaError_t launch_level( const PyrLayout& L, int o, int l, cudaTextureObject_t input_tex, float shift, bool direct_o0, bool direct_scaling,
+                                 const GaussTables& T, cudaStream_t st )
+{
+    const int ds_level = L.n_lvl - 3;      /* _levels - PREV_LEVEL, s_pyramid_build.cu:229 */
+    BlurArgs a;
+    a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
+    a.y_lo = L.cmp_lo[o]; a.y_hi = L.cmp_hi[o]; a.r_lo = L.row_lo[o]; a.r_hi = L.row_hi[o];
+    a.dst = L.base[o] + (size_t)l * L.lstride[o];
+    a.ds_dst = nullptr; a.ds_pitch = 0;
+    if( l == ds_level && o + 1 < L.alloc_end && !direct_scaling ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
+    a.shift = o == 0 ? shift : 0.5f;                          /* ScaleDirect: only octave 0 has the scaled shift, s_pyramid_build.cu:110-114 */
+    if( o == 0 && direct_o0 ) {
+        a.src = nullptr; a.tex = input_tex;
+        a.th = T.abs_o0[l]; a.tv = T.abs_o0[l];
+        return launch_blur<true>( a, st );
+    }
+    if( l == 0 ) {
+        /* ScaleDirect (s_pyramid_build.cu:499-516): horizontal pass with the octave's own table dd[o], vertical pass
+         * with inc[0] (vert_from_interm( octave, 0, .. ) reads d_gauss.inc level 0 for every octave) */
+        a.src = nullptr; a.tex = input_tex;
+        a.th = T.dd[o]; a.tv = T.inc[0];
+        return launch_blur<true>( a, st );
+    }
+    a.src = L.base[o] + (size_t)( l - 1 ) * L.lstride[o]; a.tex = 0;
+    a.th = T.inc[l]; a.tv = T.inc[l];
+    return launch_blur<false>( a, st );
+}
+
+/* the same for callers that drive the pyramid level by level (banded extraction with halo exchange, pipeline.cu) */
+cudaError_t launch_pyramid_level( const PyrLayout& L, int o, int l, cudaTextureObject_t input_tex, float shift, int gauss_mode,
+                                  const GaussTables& T, cudaStream_t st )
+{
+    if( gauss_mode != PSIFT_GAUSS_VLFEAT_COMPUTE && gauss_mode != PSIFT_GAUSS_OPENCV_COMPUTE && gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE_ALL )
+        return cudaErrorInvalidValue;
+    return launch_level( L, o, l, input_tex, shift, gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE_ALL, false, T, st );
 }
 
 cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode, int scaling_mode,
@@ -1074,30 +1114,9 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
                     side_used[o & 1] = true;
                 }
             }
-            BlurArgs a;
-            a.w = L.w[o]; a.h = L.h[o]; a.pitch = L.pitch[o];
-            a.y_lo = L.row_lo[o]; a.y_hi = L.row_hi[o];
-            a.dst = L.base[o] + (size_t)l * L.lstride[o];
-            a.ds_dst = nullptr; a.ds_pitch = 0;
-            if( l == ds_level && o + 1 < L.alloc_end && !direct_scaling ) { a.ds_dst = L.base[o + 1]; a.ds_pitch = L.pitch[o + 1]; }
-            a.shift = o == 0 ? shift : 0.5f;                          /* ScaleDirect: only octave 0 has the scaled shift, s_pyramid_build.cu:110-114 */
             const bool timed = o == 0 && S.lvl_ev != nullptr;
             if( timed && ( e = cudaEventRecord( S.lvl_ev[2 * l], st ) ) != cudaSuccess ) return e;
-            if( o == 0 && direct_o0 ) {
-                a.src = nullptr; a.tex = input_tex;
-                a.th = T.abs_o0[l]; a.tv = T.abs_o0[l];
-                e = launch_blur<true>( a, st );
-            } else if( l == 0 ) {
-                /* ScaleDirect (s_pyramid_build.cu:499-516): horizontal pass with the octave's own table dd[o], vertical pass
-                 * with inc[0] (vert_from_interm( octave, 0, .. ) reads d_gauss.inc level 0 for every octave) */
-                a.src = nullptr; a.tex = input_tex;
-                a.th = T.dd[o]; a.tv = T.inc[0];
-                e = launch_blur<true>( a, st );
-            } else {
-                a.src = L.base[o] + (size_t)( l - 1 ) * L.lstride[o]; a.tex = 0;
-                a.th = T.inc[l]; a.tv = T.inc[l];
-                e = launch_blur<false>( a, st );
-            }
+            e = launch_level( L, o, l, input_tex, shift, direct_o0, direct_scaling, T, st );
             if( e != cudaSuccess ) return e;
             if( timed && ( e = cudaEventRecord( S.lvl_ev[2 * l + 1], st ) ) != cudaSuccess ) return e;
             if( launches ) ++*launches;

@@ -26,9 +26,11 @@ struct PyrStreams {
 };
 cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, float shift, float up_pow, int gauss_mode, int scaling_mode,
                             const GaussTables& T, const PyrStreams& S, long long* launches );
+cudaError_t launch_pyramid_level( const PyrLayout& L, int o, int l, cudaTextureObject_t input_tex, float shift, int gauss_mode,
+                                  const GaussTables& T, cudaStream_t st );
 /* k_extrema.cu */
-cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted,
-                            int ext_capacity, Counters* ct, cudaStream_t st, long long* launches );
+cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted, Cand* sort_tmp,
+                            int ext_capacity, Counters* ct, SortScratch* ss, cudaStream_t st, long long* launches );
 /* k_filter.cu */
 size_t filter_scratch_bytes( int ext_capacity );
 cudaError_t launch_grid_filter( const PyrLayout& L, const psift_config& cfg, Cand* list, Cand* spare, int ext_capacity,

@@ -19,6 +19,9 @@
 #include <cstdarg>
 #include <vector>
 #include <mutex>
+#include <thread>
+#include <string>
+#include <cmath>
 #include <new>
 
 using namespace psift;
@@ -65,14 +68,14 @@ struct Slot {
     float* arena = nullptr; size_t arena_floats = 0;
     PyrLayout L;
     int in_w = 0, in_h = 0;
-    int reg_kind = 0, reg_a = 0, reg_b = 0, reg_c = 0;     /* region the layout was built for (see Region) */
+    int reg_kind = 0, reg_a = 0, reg_b = 0, reg_c = 0, reg_exchange = 0;   /* region the layout was built for (see Region) */
     std::vector<cudaTextureObject_t> lintex_h;
     cudaTextureObject_t* lintex_d = nullptr;
     std::vector<cudaTextureObject_t> scratch_tex;          /* Gauss mode "relative": the scratch plane, one view per octave */
     float* scratch = nullptr;
 
     /* keypoints */
-    Cand* cand = nullptr; Cand* sorted = nullptr;
+    Cand* cand = nullptr; Cand* sorted = nullptr; Cand* sort_tmp = nullptr;
     int cand_stride = 0, ext_cap = 0, desc_cap = 0;
     psift_extremum* ext = nullptr;
     psift_feature*  feat = nullptr;
@@ -138,7 +141,7 @@ static void free_slot( Slot& s )
     if( s.img_tex ) cudaDestroyTextureObject( s.img_tex );
     if( s.d_img ) cudaFree( s.d_img );
     if( s.h_img ) cudaFreeHost( s.h_img );
-    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
+    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
     if( s.h_ct ) cudaFreeHost( s.h_ct );
     if( s.h_ext ) cudaFreeHost( s.h_ext );
     if( s.h_feat ) cudaFreeHost( s.h_feat );
@@ -164,6 +167,8 @@ struct Region {
     int kind = 0;            /* 0 whole image, 1 band, 2 seeded upper octaves */
     int y0 = 0, y1 = 0;      /* owned rows of octave 0 */
     int split = 0;           /* band: last octave built; seeded: first octave built */
+    int exchange = 0;        /* band: 1 = the band computes its own rows only; `halo` rows above and below arrive from the
+                                neighbouring bands after every level (psift_extract_banded) */
 };
 
 /* rows of octave 0 a band must hold so that everything it owns, in every octave up to `split`, is
@@ -189,9 +194,22 @@ static int setup_pyramid( psift_ctx* c, Slot& s, int w, int h, const Region& reg
     if( rc != PSIFT_OK ) { s.in_w = s.in_h = 0; s.epoch++; }
     return rc;
 }
+/* rows a band keeps of its neighbours' planes when halos are exchanged per level: the window of the orientation /
+ * descriptor / refinement stages around a keypoint (octave pixels, the same in every octave), which is more than any
+ * filter's reach */
+static int band_exchange_rows( const psift_ctx* c )
+{
+    const int n_lvl = c->cfg.levels + 3;
+    int s_max = 0;
+    for( int l = 0; l < n_lvl; l++ ) s_max = std::max( s_max, c->gt.inc[l].span );
+    s_max = std::max( s_max, c->gt.dd[0].span );
+    const int win = (int)ceilf( 3.6f * 3.0f * c->cfg.sigma * powf( 2.0f, (float)n_lvl / (float)c->cfg.levels ) ) + 16;
+    return ( std::max( win, s_max ) + 2 + 1 ) / 2 * 2;
+}
+
 static int setup_pyramid_impl( psift_ctx* c, Slot& s, int w, int h, const Region& reg )
 {
-    if( s.in_w == w && s.in_h == h && s.arena && s.reg_kind == reg.kind && s.reg_a == reg.y0 && s.reg_b == reg.y1 && s.reg_c == reg.split ) return PSIFT_OK;
+    if( s.in_w == w && s.in_h == h && s.arena && s.reg_exchange == reg.exchange && s.reg_kind == reg.kind && s.reg_a == reg.y0 && s.reg_b == reg.y1 && s.reg_c == reg.split ) return PSIFT_OK;
     /* everything that can be refused is refused before the slot's state is touched */
     if( reg.kind == 1 && c->cfg.gauss_mode == PSIFT_GAUSS_VLFEAT_RELATIVE )
         return fail( PSIFT_E_INVALID, "the relative Gauss mode is not available for banded extraction" );
@@ -224,13 +242,21 @@ static int setup_pyramid_impl( psift_ctx* c, Slot& s, int w, int h, const Region
         if( ow < 1 || oh < 1 ) return fail( PSIFT_E_INVALID, "image %dx%d too small for %d octaves", w, h, n_oct );
         L.w[o] = ow; L.h[o] = oh;
         L.row_lo[o] = 0; L.row_hi[o] = oh; L.own_lo[o] = 0; L.own_hi[o] = oh;
-        if( reg.kind == 1 ) {
+        if( reg.kind == 1 && !reg.exchange ) {
             L.row_lo[o] = lo0 >> o;
             L.row_hi[o] = std::min( oh, o == 0 ? hi0 : ( L.row_hi[o - 1] + 1 ) >> 1 );
         }
         if( reg.kind != 0 ) {
             L.own_lo[o] = std::min( oh, reg.y0 >> o );
             L.own_hi[o] = reg.y1 >= h0 ? oh : std::min( oh, reg.y1 >> o );
+        }
+        L.cmp_lo[o] = L.row_lo[o]; L.cmp_hi[o] = L.row_hi[o];
+        if( reg.kind == 1 && reg.exchange ) {
+            /* own rows are computed here (band starts are multiples of 2^(split+1): even in every octave up to the split),
+             * the halo rows are copied in; the seed octave holds the band's own rows of level 0 */
+            const int E = o <= reg.split ? band_exchange_rows( c ) : 0;
+            L.cmp_lo[o] = L.own_lo[o]; L.cmp_hi[o] = L.own_hi[o];
+            L.row_lo[o] = std::max( 0, L.own_lo[o] - E ); L.row_hi[o] = std::min( oh, L.own_hi[o] + E );
         }
         L.pitch[o] = ( ow + 31 ) / 32 * 32;
         const bool held = o >= L.oct_begin && o < L.alloc_end;
@@ -258,7 +284,7 @@ static int setup_pyramid_impl( psift_ctx* c, Slot& s, int w, int h, const Region
     for( int o = 0; o < n_oct; o++ )
         L.base[o] = reinterpret_cast<float*>( reinterpret_cast<uintptr_t>( s.arena + off[o] ) - sizeof(float) * (size_t)L.row_lo[o] * L.pitch[o] );
     s.L = L; s.in_w = w; s.in_h = h; s.epoch++;
-    s.reg_kind = reg.kind; s.reg_a = reg.y0; s.reg_b = reg.y1; s.reg_c = reg.split;
+    s.reg_kind = reg.kind; s.reg_a = reg.y0; s.reg_b = reg.y1; s.reg_c = reg.split; s.reg_exchange = reg.exchange;
 
     if( linear_needed( c->cfg.desc_mode ) || relative ) {
         /* bilinear point-of-view of every Gaussian level (Octave::alloc_data_tex, sift_octave.cu:211-248) */
@@ -331,10 +357,11 @@ static int bind_input_texture( Slot& s, const void* dptr, size_t pitch, int w, i
  * (Pyramid::reallocExtrema, sift_pyramid.cu:179-215); psift_wait() does the same and re-runs the frame. */
 static int alloc_keypoint_buffers( Slot& s, int ext_cap, int desc_cap )
 {
-    cudaFree( s.sorted ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.filt );
-    s.sorted = nullptr; s.ext = nullptr; s.feat = nullptr; s.desc_map = nullptr; s.desc = nullptr; s.filt = nullptr;
+    cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.filt );
+    s.sort_tmp = nullptr; s.sorted = nullptr; s.ext = nullptr; s.feat = nullptr; s.desc_map = nullptr; s.desc = nullptr; s.filt = nullptr;
     s.ext_cap = ext_cap; s.desc_cap = desc_cap; s.epoch++;
     CU( cudaMalloc( &s.sorted, sizeof(Cand) * (size_t)ext_cap ) );
+    CU( cudaMalloc( &s.sort_tmp, sizeof(Cand) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.ext,    sizeof(psift_extremum) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.feat,   sizeof(psift_feature) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.desc_map, sizeof(int) * (size_t)desc_cap ) );
@@ -361,7 +388,7 @@ static int init_slot( psift_ctx* c, Slot& s )
     CU( cudaMalloc( &s.cand,   sizeof(Cand) * (size_t)me * MAX_OCT ) );
     int rc = alloc_keypoint_buffers( s, me, std::max( 2 * me, me + me / 4 ) );   /* sift_pyramid.cu:148-159 */
     if( rc ) return rc;
-    CU( cudaMalloc( &s.ct, sizeof(Counters) ) );
+    CU( cudaMalloc( &s.ct, sizeof(CountersAndSort) ) );           /* the counters, and behind them the sort's bucket counters */
     CU( cudaMallocHost( &s.h_ct, sizeof(Counters) ) );
     return PSIFT_OK;
 }
@@ -458,14 +485,17 @@ static bool graphs_enabled()
 }
 
 /* the launches of one frame, onto the slot's stream (directly, or into a stream capture) */
-static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing )
+enum { FRAME_BEGIN = 1, FRAME_PYRAMID = 2, FRAME_REST = 4, FRAME_ALL = 7 };
+static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing, int parts = FRAME_ALL )
 {
     cudaStream_t st = s.stream;
     const PyrLayout& L = s.L;
     /* stage stamps: inside a graph they must be external event-record nodes to be readable afterwards */
     auto stamp = [&]( cudaEvent_t e ) { return capturing ? cudaEventRecordWithFlags( e, st, cudaEventRecordExternal ) : cudaEventRecord( e, st ); };
+    if( parts & FRAME_BEGIN ) {
     CU( stamp( s.ev[1] ) );
-    CU( cudaMemsetAsync( s.ct, 0, sizeof(Counters), st ) );           /* reset_extrema_mgmt, sift_pyramid.cu:363-370 */
+    CU( cudaMemsetAsync( s.ct, 0, sizeof(CountersAndSort), st ) );           /* reset_extrema_mgmt, sift_pyramid.cu:363-370 */
+    }
     float shift = 0.5f;                                              /* s_pyramid_build.cu:110-114 */
     if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT )
         shift = 0.5f * powf( 2.0f, c->cfg.upscale_factor );
@@ -477,9 +507,11 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing )
         for( int k = 0; k < 2 * L.n_lvl; k++ ) if( !s.lvl_ev[k] ) CU( cudaEventCreate( &s.lvl_ev[k] ) );
         s.ps.lvl_ev = s.lvl_ev;
     }
+    if( parts & FRAME_PYRAMID )
     CU( launch_pyramid( L, s.img_tex, shift, powf( 2.0f, c->cfg.upscale_factor ), c->cfg.gauss_mode, c->cfg.scaling_mode, c->gt, s.ps, &c->launches ) );
+    if( !( parts & FRAME_REST ) ) return PSIFT_OK;
     CU( stamp( s.ev[2] ) );
-    CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.ext_cap, s.ct, st, &c->launches ) );
+    CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.sort_tmp, s.ext_cap, s.ct, &reinterpret_cast<CountersAndSort*>( s.ct )->ss, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
     CU( stamp( s.ev[3] ) );
     CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, c->n_sm * 10, st, &c->launches ) );
@@ -494,12 +526,20 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing )
 /* queue one frame on the slot's stream; the input texture is already bound.  Whole-image frames run as a CUDA graph
  * from their second use on (the first one runs as plain launches: it also sets the kernels' attributes, which must
  * not happen inside a capture); banded / seeded passes and per-level timing keep plain launches. */
-static int run_frame( psift_ctx* c, Slot& s )
+static int run_frame( psift_ctx* c, Slot& s, bool pyramid_done = false )
 {
     s.pre_ext = std::min( s.pre_ext, s.ext_cap ); s.pre_desc = std::min( s.pre_desc, s.desc_cap );
     if( s.pre_ext > 0 || s.pre_desc > 0 ) { const int rc = ensure_host_results( s, s.pre_ext, s.pre_desc ); if( rc ) return rc; }
     s.run_pre_ext = s.pre_ext; s.run_pre_desc = s.pre_desc;
     c->d2h_bytes += (long long)s.pre_ext * ( sizeof(psift_feature) + sizeof(psift_extremum) ) + (long long)s.pre_desc * 512 + sizeof(Counters);
+    if( pyramid_done ) {
+        /* the arena still holds this frame's planes (a re-run with larger keypoint buffers, or a band whose pyramid was
+         * built level by level together with its neighbours): everything from the DoG stage on */
+        const int rc = enqueue_frame( c, s, false, FRAME_BEGIN | FRAME_REST );
+        if( rc ) return rc;
+        CU( cudaEventRecord( s.ev_counters, s.stream ) );
+        return PSIFT_OK;
+    }
     const bool want_graph = graphs_enabled() && s.reg_kind == 0 && !c->time_levels && s.frames_direct > 0;
     if( want_graph && ( !s.graph || s.graph_epoch != s.epoch ) ) {
         if( s.graph ) { cudaGraphExecDestroy( s.graph ); s.graph = nullptr; }
@@ -546,7 +586,7 @@ static int settle_frame( psift_ctx* c, Slot& s )
         CU( cudaStreamSynchronize( s.stream ) );
         int rc = alloc_keypoint_buffers( s, ne, nd );
         if( rc ) return rc;
-        rc = run_frame( c, s );
+        rc = run_frame( c, s, true );
         if( rc ) return rc;
         CU( cudaEventSynchronize( s.ev_counters ) );
     }
@@ -729,10 +769,12 @@ void psift_destroy( psift_ctx* c )
 
 static thread_local bool g_pinned_source = false;          /* set by psift_submit_pinned_u8 around submit_common */
 
+/* defer: set the slot up and bring the input in, but queue no kernels: the caller (psift_extract_banded) drives the
+ * launches itself and may pass src == nullptr for a seeded pass whose plane it fills in place */
 static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pitch, int elem, bool on_device, psift_job** out,
-                          const Region& reg = Region() )
+                          const Region& reg = Region(), bool defer = false )
 {
-    if( !c || !out || !src ) return fail( PSIFT_E_INVALID, "null argument" );
+    if( !c || !out || ( !src && !( defer && reg.kind == 2 ) ) ) return fail( PSIFT_E_INVALID, "null argument" );
     if( reg.kind != 0 && ( c->cfg.gauss_mode == PSIFT_GAUSS_FIXED9 || c->cfg.gauss_mode == PSIFT_GAUSS_FIXED15 ) )
         return fail( PSIFT_E_INVALID, "banded extraction is not available for the fixed9/fixed15 Gauss modes" );
     if( reg.kind != 0 && c->cfg.scaling_mode == 1 )
@@ -761,7 +803,9 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
         /* src: level 0 of octave reg.split, whole plane, device memory, `pitch` bytes per row */
         const PyrLayout& L = s.L;
         const int o = reg.split;
+        if( !src ) { /* filled in place by the caller */ } else
         if( pitch < (size_t)L.w[o] * 4 ) return fail( PSIFT_E_INVALID, "seed plane pitch smaller than a row of octave %d (%d pixels)", o, L.w[o] );
+        if( src )
         CU( cudaMemcpy2DAsync( L.base[o], (size_t)L.pitch[o] * 4, src, pitch, (size_t)L.w[o] * 4, L.h[o], cudaMemcpyDeviceToDevice, s.stream ) );
     } else if( on_device ) {
         if( pitch % 32 || ( (uintptr_t)src % 512 ) )
@@ -790,8 +834,20 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
             s.img_cap_w = std::max( s.img_cap_w, row ); s.img_cap_h = std::max( s.img_cap_h, (size_t)h );
             CU( cudaMallocPitch( &s.d_img, &s.img_pitch, s.img_cap_w, s.img_cap_h ) );
         }
+        /* a band samples only some rows of the input: the bilinear footprint of its stored rows of octave 0 (+ a margin) */
+        int ra = 0, rb = h;
+        if( reg.kind == 1 ) {
+            float shift = 0.5f;
+            if( c->cfg.sift_mode == PSIFT_MODE_POPSIFT || c->cfg.sift_mode == PSIFT_MODE_VLFEAT ) shift = 0.5f * powf( 2.0f, c->cfg.upscale_factor );
+            const double sc = (double)h / (double)s.L.h[0];
+            ra = std::max( 0, (int)floor( ( s.L.row_lo[0] + shift ) * sc - 0.5 ) - 2 );
+            rb = std::min( h, (int)floor( ( s.L.row_hi[0] - 1 + shift ) * sc - 0.5 ) + 4 );
+        }
+        const char* src_rows = (const char*)src + (size_t)ra * pitch;
+        char*       dev_rows = (char*)s.d_img + (size_t)ra * s.img_pitch;
+        const int   nrows = rb - ra;
         /* the pinned copy has the DEVICE pitch, so that the upload is one linear transfer and not a row-by-row 2-D copy */
-        const size_t need = s.img_pitch * h;
+        const size_t need = s.img_pitch * nrows;
         if( !g_pinned_source && need > s.h_img_cap ) {
             if( s.h_img ) cudaFreeHost( s.h_img );
             CU( cudaMallocHost( &s.h_img, need ) );
@@ -799,17 +855,19 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
         }
         if( g_pinned_source ) {
             /* psift_submit_pinned_u8: the caller's buffer is page-locked and stays put until psift_wait: no private copy */
-            CU( cudaMemcpy2DAsync( s.d_img, s.img_pitch, src, pitch, row, h, cudaMemcpyHostToDevice, s.stream ) );
+            CU( cudaMemcpy2DAsync( dev_rows, s.img_pitch, src_rows, pitch, row, nrows, cudaMemcpyHostToDevice, s.stream ) );
         } else {
-            if( pitch == s.img_pitch ) memcpy( s.h_img, src, pitch * ( h - 1 ) + row );
-            else for( int y = 0; y < h; y++ ) memcpy( (char*)s.h_img + y * s.img_pitch, (const char*)src + y * pitch, row );
-            CU( cudaMemcpyAsync( s.d_img, s.h_img, need, cudaMemcpyHostToDevice, s.stream ) );
+            if( pitch == s.img_pitch ) memcpy( s.h_img, src_rows, pitch * ( nrows - 1 ) + row );
+            else for( int y = 0; y < nrows; y++ ) memcpy( (char*)s.h_img + y * s.img_pitch, src_rows + y * pitch, row );
+            CU( cudaMemcpyAsync( dev_rows, s.h_img, need, cudaMemcpyHostToDevice, s.stream ) );
         }
         rc = bind_input_texture( s, s.d_img, s.img_pitch, w, h, elem );
         if( rc ) return rc;
     }
-    rc = run_frame( c, s );
-    if( rc ) return rc;
+    if( !defer ) {
+        rc = run_frame( c, s );
+        if( rc ) return rc;
+    }
     s.busy = true;
     psift_job* j = new psift_job;
     j->ctx = c; j->slot = si; j->waited = false; j->status = PSIFT_OK;
@@ -1217,24 +1275,45 @@ int psift_dev_upload( int device, void* dev, const void* host, size_t bytes )
     return PSIFT_OK;
 }
 
-/* One giant image over the given contexts (one per GPU; several on one GPU work too), start to finish:
- * band pass on every context, the ONE exchange step (every band's rows of the seed plane go to every context's copy of
- * it: peer copies over NVLink between different GPUs), seeded pass for the octaves above the split, results merged. */
+/* One giant image over the given contexts (one per GPU; several on one GPU work too), start to finish.
+ *
+ *   1. every context gets the rows of the u8 image that its band samples (staged and uploaded by one thread per context);
+ *   2. octaves 0..split are built LEVEL BY LEVEL on all contexts together: a context computes its own rows of a level,
+ *      then pulls the `halo` rows above and below from its two neighbours (device-to-device / NVLink peer copies on its
+ *      own stream, behind an event of the neighbour's stream) - SURVEY 8e's per-level halo exchange.  The halo is as wide
+ *      as the orientation / descriptor windows, so the later stages find every row they read;
+ *   3. the band's rows of the seed plane (level 0 of octave split+1, written by the fused downscale) go straight into
+ *      every context's second slot, which finishes the small octaves un-split, keeping the keypoints it owns;
+ *   4. DoG / extrema / orientation / descriptors per band; results merged.
+ * Every pixel is computed by the same arithmetic from the same inputs as in the un-split run, so the union of the bands'
+ * keypoints is that run's result bit for bit.  PSIFT_BAND_EXCHANGE=0 (or a band thinner than the halo, or a Gauss mode
+ * that cannot be driven level by level) falls back to bands that recompute their halo (band_halo_rows). */
 namespace {
 struct BandedParts {
     std::vector<psift_feature> feat; std::vector<psift_extremum> ext; std::vector<float> desc;
     void add( const psift_result& r )
     {
         const int nd0 = (int)( desc.size() / 128 );
-        for( int i = 0; i < r.n_feat; i++ ) {
-            psift_feature f = r.feat[i]; psift_extremum e = r.ext[i];
-            for( int k = 0; k < PSIFT_MAX_ORI; k++ ) if( f.desc_idx[k] >= 0 ) f.desc_idx[k] += nd0;
-            e.idx_ori += nd0;
-            feat.push_back( f ); ext.push_back( e );
-        }
+        const size_t f0 = feat.size();
+        feat.insert( feat.end(), r.feat, r.feat + r.n_feat );
+        ext.insert( ext.end(), r.ext, r.ext + r.n_feat );
+        if( nd0 )
+            for( size_t i = f0; i < feat.size(); i++ ) {
+                for( int k = 0; k < PSIFT_MAX_ORI; k++ ) if( feat[i].desc_idx[k] >= 0 ) feat[i].desc_idx[k] += nd0;
+                ext[i].idx_ori += nd0;
+            }
         desc.insert( desc.end(), r.desc, r.desc + (size_t)r.n_desc * 128 );
     }
 };
+
+/* rows [a, b) of level l of octave o: from the neighbour's arena into mine, on my stream */
+static cudaError_t pull_rows( const PyrLayout& mine, const PyrLayout& theirs, int o, int l, int a, int b, cudaStream_t st )
+{
+    if( b <= a ) return cudaSuccess;
+    const size_t off_m = (size_t)l * mine.lstride[o]   + (size_t)a * mine.pitch[o];
+    const size_t off_t = (size_t)l * theirs.lstride[o] + (size_t)a * theirs.pitch[o];
+    return cudaMemcpyAsync( mine.base[o] + off_m, theirs.base[o] + off_t, sizeof(float) * (size_t)( b - a ) * mine.pitch[o], cudaMemcpyDefault, st );
+}
 }
 
 int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8_t* host_img, size_t pitch,
@@ -1250,51 +1329,149 @@ int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8
     int rc = psift_band_plan( &cfg, w, h, n_ctx, max_seed_pixels, &split, bounds.data() );
     if( rc ) return rc;
     out->split_octave = split;
+    const bool have_seed = split + 1 < n_oct;
 
-    BandedParts P;
-    std::vector<psift_job*> jobs( n_ctx, nullptr );
-    std::vector<float*> plane( n_ctx, nullptr );
+    /* halo exchange needs a Gauss mode that is built level by level, and bands at least as thick as the halo */
+    bool exchange = true;
+    if( const char* e = getenv( "PSIFT_BAND_EXCHANGE" ) ) exchange = atoi( e ) != 0;
+    if( cfg.gauss_mode != PSIFT_GAUSS_VLFEAT_COMPUTE && cfg.gauss_mode != PSIFT_GAUSS_OPENCV_COMPUTE && cfg.gauss_mode != PSIFT_GAUSS_VLFEAT_RELATIVE_ALL ) exchange = false;
+    const int E = band_exchange_rows( ctxs[0] );
+    for( int r = 0; r < n_ctx && n_ctx > 1; r++ ) if( ( ( bounds[r + 1] - bounds[r] ) >> split ) < E ) exchange = false;
+    out->halo_exchange = exchange ? 1 : 0;
+
+    std::vector<psift_job*> jobs( n_ctx, nullptr ), seeded( n_ctx, nullptr );
+    std::vector<cudaEvent_t> ev( n_ctx, nullptr ), ev_seed( n_ctx, nullptr );
     auto cleanup = [&]() {
         for( int r = 0; r < n_ctx; r++ ) {
             if( jobs[r] ) { psift_job_free( jobs[r] ); jobs[r] = nullptr; }
-            if( plane[r] ) { cudaSetDevice( ctxs[r]->device ); cudaFree( plane[r] ); plane[r] = nullptr; }
+            if( seeded[r] ) { psift_job_free( seeded[r] ); seeded[r] = nullptr; }
+            if( ev[r] || ev_seed[r] ) cudaSetDevice( ctxs[r]->device );
+            if( ev[r] ) { cudaEventDestroy( ev[r] ); ev[r] = nullptr; }
+            if( ev_seed[r] ) { cudaEventDestroy( ev_seed[r] ); ev_seed[r] = nullptr; }
         }
     };
-    /* band pass: all contexts work at the same time */
     for( int r = 0; r < n_ctx; r++ )
-        if( ( rc = psift_submit_band_u8( ctxs[r], w, h, host_img, pitch, 0, bounds[r], bounds[r + 1], split, &jobs[r] ) ) != PSIFT_OK ) { cleanup(); return rc; }
-    for( int r = 0; r < n_ctx; r++ ) {
-        psift_result res;
-        if( ( rc = psift_wait( jobs[r], &res ) ) != PSIFT_OK ) { cleanup(); return rc; }
-        P.add( res );
-    }
-    if( split + 1 < n_oct ) {
-        int sw = 0, sh = 0;
-        const float* rows; int pf, lo, hi;
-        if( ( rc = psift_band_seed( jobs[0], &rows, &pf, &lo, &hi, &sw, &sh ) ) != PSIFT_OK ) { cleanup(); return rc; }
-        for( int r = 0; r < n_ctx; r++ ) {
-            cudaSetDevice( ctxs[r]->device );
-            for( int q = 0; q < n_ctx; q++ )                         /* peer access where the hardware has it; else the copy is staged */
-                if( ctxs[q]->device != ctxs[r]->device ) { cudaDeviceEnablePeerAccess( ctxs[q]->device, 0 ); cudaGetLastError(); }
-            if( cudaMalloc( &plane[r], sizeof(float) * (size_t)sw * sh ) != cudaSuccess ) { cleanup(); return fail( PSIFT_E_CUDA, "seed plane: out of memory" ); }
-        }
-        /* the exchange: band r's own rows of the seed plane -> every context's plane */
-        for( int r = 0; r < n_ctx; r++ ) {
-            const int a = bounds[r] >> ( split + 1 );
-            const int b = ( r + 1 == n_ctx ) ? sh : std::min( sh, bounds[r + 1] >> ( split + 1 ) );
-            if( b <= a ) continue;
-            for( int q = 0; q < n_ctx; q++ )
-                if( ( rc = psift_band_seed_copy( jobs[r], plane[q] + (size_t)a * sw, (size_t)sw * 4, a, b ) ) != PSIFT_OK ) { cleanup(); return rc; }
-        }
-        for( int r = 0; r < n_ctx; r++ ) { psift_job_free( jobs[r] ); jobs[r] = nullptr; }
+        for( int q = 0; q < n_ctx; q++ )                                /* peer access where the hardware has it; else copies are staged */
+            if( ctxs[q]->device != ctxs[r]->device ) { cudaSetDevice( ctxs[r]->device ); cudaDeviceEnablePeerAccess( ctxs[q]->device, 0 ); cudaGetLastError(); }
+
+    /* 1. upload: one thread per context stages its band's rows into page-locked memory and queues the copy */
+    {
+        std::vector<int> rcs( n_ctx, PSIFT_OK );
+        std::vector<std::string> msgs( n_ctx );
+        std::vector<std::thread> th;
         for( int r = 0; r < n_ctx; r++ )
-            if( ( rc = psift_submit_seed_dev_f32( ctxs[r], w, h, split + 1, plane[r], (size_t)sw * 4, bounds[r], bounds[r + 1], &jobs[r] ) ) != PSIFT_OK ) { cleanup(); return rc; }
+            th.emplace_back( [&, r]() {
+                Region reg; reg.kind = 1; reg.y0 = bounds[r]; reg.y1 = bounds[r + 1]; reg.split = split; reg.exchange = exchange ? 1 : 0;
+                rcs[r] = submit_common( ctxs[r], w, h, host_img, pitch, 1, false, &jobs[r], reg, exchange );
+                if( rcs[r] != PSIFT_OK ) msgs[r] = g_err;
+            } );
+        for( auto& t : th ) t.join();
+        for( int r = 0; r < n_ctx; r++ ) if( rcs[r] != PSIFT_OK ) { cleanup(); return fail( rcs[r], "band %d: %s", r, msgs[r].c_str() ); }
+    }
+    auto slot_of = [&]( psift_job* j ) -> Slot& { return j->ctx->slots[j->slot]; };
+#define BX( call ) do { cudaError_t e_ = ( call ); if( e_ != cudaSuccess ) { cleanup(); \
+    return fail( PSIFT_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString( e_ ), __FILE__, __LINE__ ); } } while( 0 )
+    for( int r = 0; r < n_ctx; r++ ) {
+        BX( cudaSetDevice( ctxs[r]->device ) );
+        BX( cudaEventCreateWithFlags( &ev[r], cudaEventDisableTiming ) );
+        BX( cudaEventCreateWithFlags( &ev_seed[r], cudaEventDisableTiming ) );
+    }
+
+    /* 3a. the second slot of every context: the octaves above the split, from a seed plane that is filled in place */
+    if( have_seed )
         for( int r = 0; r < n_ctx; r++ ) {
-            psift_result res;
-            if( ( rc = psift_wait( jobs[r], &res ) ) != PSIFT_OK ) { cleanup(); return rc; }
-            P.add( res );
+            Region reg; reg.kind = 2; reg.y0 = bounds[r]; reg.y1 = bounds[r + 1]; reg.split = split + 1;
+            if( ( rc = submit_common( ctxs[r], w, h, nullptr, 0, 4, true, &seeded[r], reg, true ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        }
+
+    /* 2. octaves 0..split, level by level, halos pulled from the neighbours after every level */
+    if( exchange ) {
+        float shift = 0.5f;
+        if( cfg.sift_mode == PSIFT_MODE_POPSIFT || cfg.sift_mode == PSIFT_MODE_VLFEAT ) shift = 0.5f * powf( 2.0f, cfg.upscale_factor );
+        const int n_lvl = cfg.levels + 3, ds_level = n_lvl - 3;
+        for( int r = 0; r < n_ctx; r++ ) {                               /* stage stamps and counters, as enqueue_frame does */
+            Slot& s = slot_of( jobs[r] );
+            BX( cudaSetDevice( ctxs[r]->device ) );
+            BX( cudaEventRecord( s.ev[1], s.stream ) );
+        }
+        for( int o = 0; o <= split; o++ )
+            for( int l = ( o == 0 ? 0 : 1 ); l < n_lvl; l++ ) {
+                for( int r = 0; r < n_ctx; r++ ) {
+                    Slot& s = slot_of( jobs[r] );
+                    BX( cudaSetDevice( ctxs[r]->device ) );
+                    BX( launch_pyramid_level( s.L, o, l, s.img_tex, shift, cfg.gauss_mode, ctxs[r]->gt, s.stream ) );
+                    ctxs[r]->launches++;
+                    BX( cudaEventRecord( ev[r], s.stream ) );
+                }
+                for( int r = 0; r < n_ctx; r++ ) {
+                    Slot& s = slot_of( jobs[r] );
+                    BX( cudaSetDevice( ctxs[r]->device ) );
+                    for( int d = -1; d <= 1; d += 2 ) {
+                        const int q = r + d;
+                        if( q < 0 || q >= n_ctx ) continue;
+                        const PyrLayout& T = slot_of( jobs[q] ).L;
+                        BX( cudaStreamWaitEvent( s.stream, ev[q], 0 ) );
+                        if( d < 0 ) BX( pull_rows( s.L, T, o, l, s.L.row_lo[o], s.L.cmp_lo[o], s.stream ) );
+                        else        BX( pull_rows( s.L, T, o, l, s.L.cmp_hi[o], s.L.row_hi[o], s.stream ) );
+                        if( l == ds_level && o < split ) {               /* the fused downscale wrote level 0 of the next octave */
+                            if( d < 0 ) BX( pull_rows( s.L, T, o + 1, 0, s.L.row_lo[o + 1], s.L.cmp_lo[o + 1], s.stream ) );
+                            else        BX( pull_rows( s.L, T, o + 1, 0, s.L.cmp_hi[o + 1], s.L.row_hi[o + 1], s.stream ) );
+                        }
+                    }
+                }
+                /* 3b. the seed rows exist as soon as level `ds_level` of the split octave does: send them on, ahead of the
+                 * remaining levels */
+                if( have_seed && o == split && l == ds_level )
+                    for( int r = 0; r < n_ctx; r++ ) {
+                        Slot& s = slot_of( jobs[r] );
+                        const int so = split + 1;
+                        BX( cudaSetDevice( ctxs[r]->device ) );
+                        for( int q = 0; q < n_ctx; q++ )
+                            BX( pull_rows( slot_of( seeded[q] ).L, s.L, so, 0, s.L.cmp_lo[so], s.L.cmp_hi[so], s.stream ) );
+                        BX( cudaEventRecord( ev_seed[r], s.stream ) );
+                    }
+            }
+        for( int r = 0; r < n_ctx; r++ ) {
+            BX( cudaSetDevice( ctxs[r]->device ) );
+            if( ( rc = run_frame( ctxs[r], slot_of( jobs[r] ), true ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        }
+    } else if( have_seed ) {
+        /* bands that recomputed their halo ran as ordinary jobs: their seed rows follow everything else on their stream */
+        for( int r = 0; r < n_ctx; r++ ) {
+            Slot& s = slot_of( jobs[r] );
+            const int so = split + 1;
+            const int a = bounds[r] >> so, b = ( r + 1 == n_ctx ) ? s.L.h[so] : std::min( s.L.h[so], bounds[r + 1] >> so );
+            BX( cudaSetDevice( ctxs[r]->device ) );
+            for( int q = 0; q < n_ctx; q++ )
+                BX( pull_rows( slot_of( seeded[q] ).L, s.L, so, 0, a, b, s.stream ) );
+            BX( cudaEventRecord( ev_seed[r], s.stream ) );
         }
     }
+    /* 3c. the small octaves, once every band's seed rows have arrived */
+    if( have_seed )
+        for( int r = 0; r < n_ctx; r++ ) {
+            Slot& s = slot_of( seeded[r] );
+            BX( cudaSetDevice( ctxs[r]->device ) );
+            for( int q = 0; q < n_ctx; q++ ) BX( cudaStreamWaitEvent( s.stream, ev_seed[q], 0 ) );
+            if( ( rc = run_frame( ctxs[r], s ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        }
+#undef BX
+
+    /* 4. results */
+    BandedParts P;
+    long long tf = 0, td = 0;
+    std::vector<psift_result> res( 2 * n_ctx );
+    for( int r = 0; r < n_ctx; r++ ) {
+        if( ( rc = psift_wait( jobs[r], &res[r] ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        tf += res[r].n_feat; td += res[r].n_desc;
+    }
+    for( int r = 0; r < n_ctx && have_seed; r++ ) {
+        if( ( rc = psift_wait( seeded[r], &res[n_ctx + r] ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        tf += res[n_ctx + r].n_feat; td += res[n_ctx + r].n_desc;
+    }
+    P.feat.reserve( (size_t)tf ); P.ext.reserve( (size_t)tf ); P.desc.reserve( (size_t)td * 128 );
+    for( int r = 0; r < n_ctx; r++ ) P.add( res[r] );
+    for( int r = 0; r < n_ctx && have_seed; r++ ) P.add( res[n_ctx + r] );
     cleanup();
     out->n_feat = (int)P.feat.size(); out->n_desc = (int)( P.desc.size() / 128 );
     out->feat = (psift_feature*)malloc( sizeof(psift_feature) * std::max<size_t>( P.feat.size(), 1 ) );

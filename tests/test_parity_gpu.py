@@ -400,27 +400,40 @@ def test_banded_equals_whole(w, h, parts, seed_px, flags):
     assert da == db
 
 
-def test_extract_banded_one_call():
-    """psift_extract_banded (three contexts on this GPU; on a multi-GPU box they would be one per GPU and the seed rows
-    would travel as peer copies): the merged keypoints equal the un-split run's, record for record."""
-    img = synth.gen(1024, 768, 7)
-    cfg = capi.default_config(downsampling=0)
+def _canon_merged(ex):
+    o = np.lexsort((ex.feat["x"], ex.feat["y"], ex.feat["sigma"], ex.feat["octave"]))
+    f = ex.feat[o]
+    d = np.stack([ex.desc[f["desc_idx"][:, k].clip(0)] * (f["desc_idx"][:, k:k + 1] >= 0) for k in range(4)], 1)
+    rec = [f[n].tobytes() for n in ("octave", "x", "y", "sigma", "num_ori", "ori")]
+    return rec, d.tobytes()
+
+
+@pytest.mark.parametrize("w,h,seed,n_ctx,seed_px,flags,exchange", [
+    (1024, 768, 7, 3, 128 * 96, ["--downsampling", "0"], 0),        # bands thinner than the halo: every band recomputes its halo
+    (768, 3072, 8, 3, 192 * 768, ["--downsampling", "0"], 1),       # split 1, three bands of 1024 rows: halos exchanged per level
+    (512, 1280, 9, 2, 128 * 320, [], 1),                             # default Config (2x upscale), split 2, two bands
+    (640, 2560, 10, 4, 320 * 1280, ["--downsampling", "0", "--mode", "vlfeat", "--desc-mode", "grid"], 1),   # split 0
+    (600, 2048, 11, 2, 1, ["--downsampling", "0", "--mode", "opencv", "--gauss-mode", "opencv"], None),      # deepest split the planner allows
+])
+def test_extract_banded_one_call(w, h, seed, n_ctx, seed_px, flags, exchange):
+    """psift_extract_banded (several contexts on this GPU; on a multi-GPU box they are one per GPU and the halo and seed
+    rows travel as peer copies): the merged keypoints equal the un-split run's, record for record and descriptor for
+    descriptor, with per-level halo exchange as well as with recomputed halos."""
+    img = synth.gen(w, h, seed)
+    cfg = capi.config_from_flags(flags)
     with capi.Context(cfg) as ctx:
         whole = ctx.extract(img)
-    ctxs = [capi.Context(cfg) for _ in range(3)]
+    ctxs = [capi.Context(cfg) for _ in range(n_ctx)]
     try:
-        got = capi.extract_banded(ctxs, img, max_seed_pixels=128 * 96)
+        got = capi.extract_banded(ctxs, img, max_seed_pixels=seed_px)
+        again = capi.extract_banded(ctxs, img, max_seed_pixels=seed_px)      # the slots are reused: no stale halo rows
     finally:
         for c in ctxs: c.close()
-    assert got.split >= 1 and got.n_feat == whole.n_feat and got.n_desc == whole.n_desc
-    def canon(ex):
-        o = np.lexsort((ex.feat["x"], ex.feat["y"], ex.feat["sigma"], ex.feat["octave"]))
-        f = ex.feat[o]
-        d = np.stack([ex.desc[f["desc_idx"][:, k].clip(0)] * (f["desc_idx"][:, k:k + 1] >= 0) for k in range(4)], 1)
-        rec = [f[n].tobytes() for n in ("octave", "x", "y", "sigma", "num_ori", "ori")]
-        return rec, d.tobytes()
-    a, b = canon(got), canon(whole)
+    if exchange is not None: assert got.halo_exchange == exchange, (got.halo_exchange, got.split)
+    assert got.n_feat == whole.n_feat and got.n_desc == whole.n_desc, (got.n_feat, whole.n_feat, got.split)
+    a, b, c2 = _canon_merged(got), _canon_merged(whole), _canon_merged(again)
     assert a[0] == b[0] and a[1] == b[1]
+    assert c2[0] == b[0] and c2[1] == b[1]
 
 
 def test_keypoint_buffers_grow():
