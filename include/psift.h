@@ -244,13 +244,14 @@ int  psift_submit_seed_dev_f32( psift_ctx* ctx, int w, int h, int first_octave, 
 
 /* The whole of the above in one call: band pass on every context, exchange of the seed rows (device-to-device; peer
  * copies over NVLink between GPUs), seeded pass, merge.  ctxs: n_ctx contexts with the SAME configuration, normally one
- * per GPU (several on one GPU work too).  The result arrays are malloc'ed: psift_banded_free. */
+ * per GPU (several on one GPU work too).  The result arrays are page-locked memory owned by the result: psift_banded_free. */
 typedef struct psift_banded_result {
     int n_feat, n_desc, split_octave;
     psift_feature*  feat;
     psift_extremum* ext;
     float*          desc;
     int             halo_exchange;   /* 1: halos were exchanged per level between neighbouring bands; 0: every band recomputed its halo */
+    void*           block;           /* owner of the three arrays (page-locked, recycled): released by psift_banded_free */
 } psift_banded_result;
 int  psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8_t* host_img, size_t pitch,
                            int max_seed_pixels, psift_banded_result* out );

@@ -44,7 +44,7 @@ FSORT = {"random": 0, "down": 1, "up": 2}   # reference sift_conf.cu:131-141 (up
 class BandedResult(C.Structure):
     """psift_banded_result (psift.h)"""
     _fields_ = [("n_feat", C.c_int), ("n_desc", C.c_int), ("split_octave", C.c_int),
-                ("feat", C.c_void_p), ("ext", C.c_void_p), ("desc", C.c_void_p), ("halo_exchange", C.c_int)]
+                ("feat", C.c_void_p), ("ext", C.c_void_p), ("desc", C.c_void_p), ("halo_exchange", C.c_int), ("block", C.c_void_p)]
 
 
 class DevInfo(C.Structure):
@@ -362,15 +362,16 @@ class BandedExtraction:
         self.desc = arr(r.desc, r.n_desc * 128, np.dtype("<f4")).reshape(-1, 128) if r.n_desc else np.zeros((0, 128), np.float32)
 
 
-def extract_banded(contexts, img, max_seed_pixels=0):
-    """One giant image over several contexts (psift_extract_banded): band pass, seed exchange, upper octaves, merge."""
+def extract_banded(contexts, img, max_seed_pixels=0, copy=True):
+    """One giant image over several contexts (psift_extract_banded): band pass with halo exchange, seed gather, upper
+    octaves, merge.  copy=False: only (n_feat, n_desc, split, halo_exchange), for timing."""
     img = np.ascontiguousarray(img, np.uint8)
     h, w = img.shape
     hs = (C.c_void_p * len(contexts))(*[c._h for c in contexts])
     r = BandedResult()
     _chk(lib().psift_extract_banded(hs, len(contexts), w, h, img.ctypes.data, w, max_seed_pixels, C.byref(r)))
     try:
-        return BandedExtraction(r)
+        return BandedExtraction(r) if copy else (r.n_feat, r.n_desc, r.split_octave, r.halo_exchange)
     finally:
         lib().psift_banded_free(C.byref(r))
 

@@ -19,6 +19,7 @@
 #include <cstdarg>
 #include <vector>
 #include <mutex>
+#include <chrono>
 #include <thread>
 #include <string>
 #include <cmath>
@@ -529,6 +530,7 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing, int parts = FRA
 static int run_frame( psift_ctx* c, Slot& s, bool pyramid_done = false )
 {
     s.pre_ext = std::min( s.pre_ext, s.ext_cap ); s.pre_desc = std::min( s.pre_desc, s.desc_cap );
+    if( s.reg_kind != 0 ) s.pre_ext = s.pre_desc = 0;      /* parts of a banded image: whoever merges them places the download */
     if( s.pre_ext > 0 || s.pre_desc > 0 ) { const int rc = ensure_host_results( s, s.pre_ext, s.pre_desc ); if( rc ) return rc; }
     s.run_pre_ext = s.pre_ext; s.run_pre_desc = s.pre_desc;
     c->d2h_bytes += (long long)s.pre_ext * ( sizeof(psift_feature) + sizeof(psift_extremum) ) + (long long)s.pre_desc * 512 + sizeof(Counters);
@@ -767,6 +769,23 @@ void psift_destroy( psift_ctx* c )
     delete c;
 }
 
+/* rows of a host image into the page-locked staging buffer; large images are copied by several threads (one core moves
+ * about 5 GB/s, a 16384 x 16384 image is 268 MB) */
+static void stage_rows( char* dst, size_t dpitch, const char* src, size_t spitch, size_t row_bytes, int nrows )
+{
+    auto part = [=]( int y0, int y1 ) {
+        if( spitch == dpitch && y1 > y0 ) memcpy( dst + (size_t)y0 * dpitch, src + (size_t)y0 * spitch, spitch * (size_t)( y1 - y0 - 1 ) + row_bytes );
+        else for( int y = y0; y < y1; y++ ) memcpy( dst + (size_t)y * dpitch, src + (size_t)y * spitch, row_bytes );
+    };
+    const size_t bytes = row_bytes * (size_t)nrows;
+    int nt = (int)std::min<size_t>( 8, bytes >> 24 );                       /* one thread per 16 MB, at most 8 */
+    nt = std::min<int>( nt, std::max( 1u, std::thread::hardware_concurrency() ) );
+    if( nt < 2 ) { part( 0, nrows ); return; }
+    std::vector<std::thread> th;
+    for( int t = 0; t < nt; t++ ) th.emplace_back( part, (int)( (long long)nrows * t / nt ), (int)( (long long)nrows * ( t + 1 ) / nt ) );
+    for( auto& t : th ) t.join();
+}
+
 static thread_local bool g_pinned_source = false;          /* set by psift_submit_pinned_u8 around submit_common */
 
 /* defer: set the slot up and bring the input in, but queue no kernels: the caller (psift_extract_banded) drives the
@@ -789,12 +808,11 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
     std::lock_guard<std::mutex> lk( c->mu );
     CU( cudaSetDevice( c->device ) );
     int si = -1;
-    for( size_t k = 0; k < c->slots.size(); k++ ) {
-        const int cand = ( c->next_slot + (int)k ) % (int)c->slots.size();
-        if( !c->slots[cand].busy ) { si = cand; break; }
-    }
+    /* the lowest free slot: a caller with one frame in flight keeps using one arena, staging buffer and result block
+     * (a 16384 x 16384 frame owns 9 GB of them) instead of allocating them afresh on every slot in turn */
+    for( size_t k = 0; k < c->slots.size(); k++ )
+        if( !c->slots[k].busy ) { si = (int)k; break; }
     if( si < 0 ) return fail( PSIFT_E_STATE, "all %d frame slots are in flight: wait for and free a job first", (int)c->slots.size() );
-    c->next_slot = ( si + 1 ) % (int)c->slots.size();
     Slot& s = c->slots[si];
     int rc = setup_pyramid( c, s, w, h, reg );
     if( rc ) return rc;
@@ -857,8 +875,7 @@ static int submit_common( psift_ctx* c, int w, int h, const void* src, size_t pi
             /* psift_submit_pinned_u8: the caller's buffer is page-locked and stays put until psift_wait: no private copy */
             CU( cudaMemcpy2DAsync( dev_rows, s.img_pitch, src_rows, pitch, row, nrows, cudaMemcpyHostToDevice, s.stream ) );
         } else {
-            if( pitch == s.img_pitch ) memcpy( s.h_img, src_rows, pitch * ( nrows - 1 ) + row );
-            else for( int y = 0; y < nrows; y++ ) memcpy( (char*)s.h_img + y * s.img_pitch, src_rows + y * pitch, row );
+            stage_rows( (char*)s.h_img, s.img_pitch, src_rows, pitch, row, nrows );
             CU( cudaMemcpyAsync( dev_rows, s.h_img, need, cudaMemcpyHostToDevice, s.stream ) );
         }
         rc = bind_input_texture( s, s.d_img, s.img_pitch, w, h, elem );
@@ -1289,23 +1306,6 @@ int psift_dev_upload( int device, void* dev, const void* host, size_t bytes )
  * keypoints is that run's result bit for bit.  PSIFT_BAND_EXCHANGE=0 (or a band thinner than the halo, or a Gauss mode
  * that cannot be driven level by level) falls back to bands that recompute their halo (band_halo_rows). */
 namespace {
-struct BandedParts {
-    std::vector<psift_feature> feat; std::vector<psift_extremum> ext; std::vector<float> desc;
-    void add( const psift_result& r )
-    {
-        const int nd0 = (int)( desc.size() / 128 );
-        const size_t f0 = feat.size();
-        feat.insert( feat.end(), r.feat, r.feat + r.n_feat );
-        ext.insert( ext.end(), r.ext, r.ext + r.n_feat );
-        if( nd0 )
-            for( size_t i = f0; i < feat.size(); i++ ) {
-                for( int k = 0; k < PSIFT_MAX_ORI; k++ ) if( feat[i].desc_idx[k] >= 0 ) feat[i].desc_idx[k] += nd0;
-                ext[i].idx_ori += nd0;
-            }
-        desc.insert( desc.end(), r.desc, r.desc + (size_t)r.n_desc * 128 );
-    }
-};
-
 /* rows [a, b) of level l of octave o: from the neighbour's arena into mine, on my stream */
 static cudaError_t pull_rows( const PyrLayout& mine, const PyrLayout& theirs, int o, int l, int a, int b, cudaStream_t st )
 {
@@ -1339,6 +1339,11 @@ int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8
     for( int r = 0; r < n_ctx && n_ctx > 1; r++ ) if( ( ( bounds[r + 1] - bounds[r] ) >> split ) < E ) exchange = false;
     out->halo_exchange = exchange ? 1 : 0;
 
+    static const bool trace = getenv( "PSIFT_BAND_TRACE" ) != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto lap = [&]( const char* what ) {
+        if( trace ) fprintf( stderr, "[banded] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>( std::chrono::steady_clock::now() - t_begin ).count() );
+    };
     std::vector<psift_job*> jobs( n_ctx, nullptr ), seeded( n_ctx, nullptr );
     std::vector<cudaEvent_t> ev( n_ctx, nullptr ), ev_seed( n_ctx, nullptr );
     auto cleanup = [&]() {
@@ -1354,6 +1359,7 @@ int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8
         for( int q = 0; q < n_ctx; q++ )                                /* peer access where the hardware has it; else copies are staged */
             if( ctxs[q]->device != ctxs[r]->device ) { cudaSetDevice( ctxs[r]->device ); cudaDeviceEnablePeerAccess( ctxs[q]->device, 0 ); cudaGetLastError(); }
 
+    lap( "plan, peer access" );
     /* 1. upload: one thread per context stages its band's rows into page-locked memory and queues the copy */
     {
         std::vector<int> rcs( n_ctx, PSIFT_OK );
@@ -1368,6 +1374,7 @@ int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8
         for( auto& t : th ) t.join();
         for( int r = 0; r < n_ctx; r++ ) if( rcs[r] != PSIFT_OK ) { cleanup(); return fail( rcs[r], "band %d: %s", r, msgs[r].c_str() ); }
     }
+    lap( "band slots, staging, upload" );
     auto slot_of = [&]( psift_job* j ) -> Slot& { return j->ctx->slots[j->slot]; };
 #define BX( call ) do { cudaError_t e_ = ( call ); if( e_ != cudaSuccess ) { cleanup(); \
     return fail( PSIFT_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString( e_ ), __FILE__, __LINE__ ); } } while( 0 )
@@ -1384,6 +1391,7 @@ int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8
             if( ( rc = submit_common( ctxs[r], w, h, nullptr, 0, 4, true, &seeded[r], reg, true ) ) != PSIFT_OK ) { cleanup(); return rc; }
         }
 
+    lap( "events, seeded slots" );
     /* 2. octaves 0..split, level by level, halos pulled from the neighbours after every level */
     if( exchange ) {
         float shift = 0.5f;
@@ -1447,6 +1455,7 @@ int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8
             BX( cudaEventRecord( ev_seed[r], s.stream ) );
         }
     }
+    lap( "levels + exchange queued" );
     /* 3c. the small octaves, once every band's seed rows have arrived */
     if( have_seed )
         for( int r = 0; r < n_ctx; r++ ) {
@@ -1457,36 +1466,66 @@ int psift_extract_banded( psift_ctx** ctxs, int n_ctx, int w, int h, const uint8
         }
 #undef BX
 
-    /* 4. results */
-    BandedParts P;
+    lap( "seeded passes queued" );
+    /* 4. results: once every part's counters are known, each part's records and descriptors are downloaded straight to
+     * their place in ONE page-locked block from the recycled pool (no merge copy); descriptor indices are re-based there */
     long long tf = 0, td = 0;
-    std::vector<psift_result> res( 2 * n_ctx );
-    for( int r = 0; r < n_ctx; r++ ) {
-        if( ( rc = psift_wait( jobs[r], &res[r] ) ) != PSIFT_OK ) { cleanup(); return rc; }
-        tf += res[r].n_feat; td += res[r].n_desc;
+    const int n_parts = have_seed ? 2 * n_ctx : n_ctx;
+    std::vector<long long> f0( n_parts + 1, 0 ), d0( n_parts + 1, 0 );
+    std::vector<int> nf( n_parts, 0 ), nd( n_parts, 0 );
+    auto part_job = [&]( int k ) { return k < n_ctx ? jobs[k] : seeded[k - n_ctx]; };
+    for( int k = 0; k < n_parts; k++ ) {
+        psift_job* j = part_job( k );
+        Slot& s = slot_of( j );
+        cudaSetDevice( j->ctx->device );
+        if( ( rc = settle_frame( j->ctx, s ) ) != PSIFT_OK ) { cleanup(); return rc; }
+        nf[k] = s.h_ct->ext_total; nd[k] = s.h_ct->ori_total;
+        f0[k] = tf; d0[k] = td;
+        tf += nf[k]; td += nd[k];
     }
-    for( int r = 0; r < n_ctx && have_seed; r++ ) {
-        if( ( rc = psift_wait( seeded[r], &res[n_ctx + r] ) ) != PSIFT_OK ) { cleanup(); return rc; }
-        tf += res[n_ctx + r].n_feat; td += res[n_ctx + r].n_desc;
+    lap( "all parts finished" );
+    psift_result_block* blk = result_pool().get( (int)std::max<long long>( tf, 1 ), (int)std::max<long long>( td, 1 ) );
+    if( !blk ) { cleanup(); return fail( PSIFT_E_CUDA, "out of page-locked host memory for %lld keypoints / %lld descriptors", tf, td ); }
+    cudaError_t ce = cudaSuccess;
+    for( int k = 0; k < n_parts && ce == cudaSuccess; k++ ) {
+        psift_job* j = part_job( k );
+        Slot& s = slot_of( j );
+        cudaSetDevice( j->ctx->device );
+        if( nf[k] > 0 ) {
+            ce = cudaMemcpyAsync( blk->feat + f0[k], s.feat, sizeof(psift_feature) * (size_t)nf[k], cudaMemcpyDeviceToHost, s.stream );
+            if( ce == cudaSuccess ) ce = cudaMemcpyAsync( blk->ext + f0[k], s.ext, sizeof(psift_extremum) * (size_t)nf[k], cudaMemcpyDeviceToHost, s.stream );
+        }
+        if( ce == cudaSuccess && nd[k] > 0 )
+            ce = cudaMemcpyAsync( blk->desc + (size_t)128 * d0[k], s.desc, sizeof(float) * 128 * (size_t)nd[k], cudaMemcpyDeviceToHost, s.stream );
+        j->ctx->d2h_bytes += (long long)nf[k] * ( sizeof(psift_feature) + sizeof(psift_extremum) ) + (long long)nd[k] * 512;
     }
-    P.feat.reserve( (size_t)tf ); P.ext.reserve( (size_t)tf ); P.desc.reserve( (size_t)td * 128 );
-    for( int r = 0; r < n_ctx; r++ ) P.add( res[r] );
-    for( int r = 0; r < n_ctx && have_seed; r++ ) P.add( res[n_ctx + r] );
+    for( int k = 0; k < n_parts && ce == cudaSuccess; k++ ) {
+        psift_job* j = part_job( k );
+        cudaSetDevice( j->ctx->device );
+        ce = cudaStreamSynchronize( slot_of( j ).stream );
+    }
+    if( ce != cudaSuccess ) { cudaGetLastError(); result_pool().put( blk ); cleanup(); return fail( PSIFT_E_CUDA, "result download: %s", cudaGetErrorString( ce ) ); }
+    lap( "downloaded" );
+    for( int k = 1; k < n_parts; k++ ) {
+        const int base = (int)d0[k];
+        if( !base ) continue;
+        psift_feature* f = blk->feat + f0[k]; psift_extremum* e = blk->ext + f0[k];
+        for( int i = 0; i < nf[k]; i++ ) {
+            for( int q = 0; q < PSIFT_MAX_ORI; q++ ) if( f[i].desc_idx[q] >= 0 ) f[i].desc_idx[q] += base;
+            e[i].idx_ori += base;
+        }
+    }
+    out->n_feat = (int)tf; out->n_desc = (int)td;
+    out->feat = blk->feat; out->ext = blk->ext; out->desc = blk->desc; out->block = blk;
+    lap( "re-based" );
     cleanup();
-    out->n_feat = (int)P.feat.size(); out->n_desc = (int)( P.desc.size() / 128 );
-    out->feat = (psift_feature*)malloc( sizeof(psift_feature) * std::max<size_t>( P.feat.size(), 1 ) );
-    out->ext  = (psift_extremum*)malloc( sizeof(psift_extremum) * std::max<size_t>( P.ext.size(), 1 ) );
-    out->desc = (float*)malloc( sizeof(float) * std::max<size_t>( P.desc.size(), 1 ) );
-    if( !out->feat || !out->ext || !out->desc ) { psift_banded_free( out ); return fail( PSIFT_E_INVALID, "out of host memory" ); }
-    if( !P.feat.empty() ) { memcpy( out->feat, P.feat.data(), sizeof(psift_feature) * P.feat.size() ); memcpy( out->ext, P.ext.data(), sizeof(psift_extremum) * P.ext.size() ); }
-    if( !P.desc.empty() ) memcpy( out->desc, P.desc.data(), sizeof(float) * P.desc.size() );
     return PSIFT_OK;
 }
 
 void psift_banded_free( psift_banded_result* r )
 {
     if( !r ) return;
-    free( r->feat ); free( r->ext ); free( r->desc );
+    result_pool().put( (psift_result_block*)r->block );       /* the arrays live in a page-locked block of the recycled pool */
     memset( r, 0, sizeof *r );
 }
 
