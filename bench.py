@@ -155,6 +155,70 @@ def cpu_baseline():
             "sample": "1 frame 1920x1080 (seed 1000), default Config, single-thread C++ restatement of the reference kernels (the reference has no CPU path); %.1f s" % dt}
 
 
+TILED = 16384          # BASELINE.json configs[4]: one 16384 x 16384 image, --downsampling 0
+
+
+def giant_image():
+    """16384 x 16384 synthetic image: an 8 x 8 mosaic of one 2048 x 2048 synth.gen() tile (generating 268 Mpx of
+    independent content takes minutes; equality with the un-split run does not depend on the content)"""
+    import numpy as np
+    from popsift_b200 import synth
+    return np.tile(synth.gen(2048, 2048, 5), (TILED // 2048, TILED // 2048))
+
+
+def tiled_leg(n_gpus, steps=8, warmup=2):
+    """BASELINE config 5 through psift_extract_banded: one context per GPU of THIS process, row bands with per-level halo
+    exchange over NVLink, host image in, merged host results out; wall clock per image, next to the un-split run on
+    one GPU; equality of the two results (order-independent digests) is asserted."""
+    from popsift_b200 import capi, banded
+    img = giant_image()
+    cfg = capi.default_config(downsampling=0); cfg.max_extrema = 400000
+    with capi.Context(cfg, device=0) as ctx:
+        whole = ctx.extract(img)
+        for _ in range(warmup):
+            j = ctx.submit(img); ctx.wait(j, copy=False); ctx.free(j)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            j = ctx.submit(img); ctx.wait(j, copy=False); ctx.free(j)
+        t_whole = (time.perf_counter() - t0) / steps
+        stage = ctx.timing()
+    want = (whole.n_feat, whole.n_desc) + banded.digest(whole)
+    n_ctx = max(n_gpus, 2)                    # on one GPU: two bands on the same device (exercises the exchange path)
+    ctxs = [capi.Context(cfg, device=i % n_gpus) for i in range(n_ctx)]
+    try:
+        got = capi.extract_banded(ctxs, img)
+        same = (got.n_feat, got.n_desc) + banded.digest(got) == want
+        for _ in range(warmup): capi.extract_banded(ctxs, img, copy=False)
+        t0 = time.perf_counter()
+        for _ in range(steps): capi.extract_banded(ctxs, img, copy=False)
+        t_band = (time.perf_counter() - t0) / steps
+    finally:
+        for c in ctxs: c.close()
+    assert same, "banded result differs from the un-split run"
+    return {"workload": "one 16384x16384 u8 image, default Config with --downsampling 0 (12 octaves), host image in, host results out",
+            "n_gpus": n_gpus, "bands": n_ctx, "halo_exchange": got.halo_exchange, "split_octave": got.split,
+            "ms_per_image": 1e3 * t_band, "images_per_sec": 1.0 / t_band,
+            "unsplit_1gpu_ms_per_image": 1e3 * t_whole, "speedup_vs_unsplit": t_whole / t_band,
+            "unsplit_stage_ms": {k: round(v, 3) for k, v in stage.items()},
+            "keypoints": whole.n_feat, "descriptors": whole.n_desc, "equal_to_unsplit": bool(same), "steps": steps, "timing": "wall clock"}
+
+
+def bench_tiled(args, rank, world):
+    """--workload tiled16k: config 5 alone.  One process drives all N GPUs (the bands of one image cooperate), so under
+    torchrun rank 0 runs and the other ranks exit."""
+    if rank != 0:
+        return
+    t = tiled_leg(args.gpus, steps=max(args.steps, 1), warmup=max(args.warmup, 1))
+    line = {"metric": "images_per_sec_16384_tiled", "value": t["images_per_sec"], "unit": "images/s", "n_gpus": args.gpus, "steps": t["steps"],
+            "warmup": max(args.warmup, 1), "ms_per_step": t["ms_per_image"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": t["workload"], "bands": t["bands"]},
+            "e2e": {"value": t["images_per_sec"], "unit": "images/s", "h2d_bytes_per_step": TILED * TILED,
+                    "d2h_bytes_per_step": t["keypoints"] * 96 + t["descriptors"] * 512,
+                    "note": "the tiled entry point takes a host image and returns host results: value and e2e are the same host-to-host figure"},
+            "tiled": t}
+    print(json.dumps(line))
+
+
 def bench_reference(args, rank):
     if rank != 0:
         return
@@ -202,10 +266,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--workload", default="stream1080p", help="stream1080p (default, BASELINE configs[3]) or tiled16k (configs[4])")
+    ap.add_argument("--no-tiled", action="store_true", help="skip the giant-image leg of the default workload")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
         bench_reference(args, rank)
+        return
+    if args.workload == "tiled16k":
+        bench_tiled(args, rank, world)
         return
 
     import numpy as np
@@ -269,12 +338,13 @@ def main():
     # from rank 0 while the other ranks wait
     one_object = None
     if world > 1:
+        torch.cuda.synchronize(); pdist.cpu_barrier()        # the other ranks wait on the CPU: their GPUs must be idle
         if rank == 0:
             r1 = capi.cxx_stream(imgs, args.warmup * BATCH * world, n_frames * world, first_device=0, n_devices=world,
                                  n_producers=CXX_PRODUCERS * world, window=CXX_WINDOW)
             one_object = {"value": r1["images_per_sec"], "unit": "images/s", "devices": r1["devices"], "producer_threads": CXX_PRODUCERS * world,
                           "what": "one PopSift object dispatching to all GPUs of this process (rank 0; the other ranks idle), wall clock"}
-        barrier()
+        pdist.cpu_barrier()
 
     # kernel-stage times (CUDA events on the frame's stream), one frame at a time, warm
     stage = {}
@@ -337,6 +407,17 @@ def main():
                     "per_level_ms": [float(x) for x in lv_alone], "per_level_ms_stream_full": [float(x) for x in lv], "per_level_bytes": lvl_bytes,
                     "timing": "CUDA events on the stream each launch goes to (psift_debug_time_levels), frames one at a time; *_stream_full: all frame slots busy"}}
 
+    # BASELINE config 5 (one giant image over the GPUs of the box), driven from rank 0 while the other ranks wait
+    tiled = None
+    if not args.no_tiled:
+        torch.cuda.synchronize(); pdist.cpu_barrier()
+        if rank == 0:
+            try:
+                tiled = tiled_leg(world)
+            except Exception as e:                  # the headline line must not depend on this leg
+                tiled = {"error": repr(e)[:300]}
+        pdist.cpu_barrier()
+
     if rank == 0:
         line = {"metric": "images_per_sec_1080p", "value": world * n_frames / dt_dev, "unit": "images/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt_dev / args.steps,
@@ -360,6 +441,7 @@ def main():
                 "stage_ms": stage,
                 "roofline": roofline,
                 "cpu_baseline": cpu_baseline() if not args.no_cpu else {"value": None, "unit": "images/s", "cores": 1, "kind": "port", "sample": "skipped (--no-cpu)"},
+                "tiled16k": tiled,
                 "clocks": cs.summary()}
         print(json.dumps(line))
     ctx.close()

@@ -27,6 +27,22 @@ def barrier():
         torch.cuda.synchronize()
 
 
+_cpu_group = None
+
+
+def cpu_barrier():
+    """Barrier that waits on the CPU (a gloo group next to the NCCL one): for the legs in which rank 0 alone drives every
+    GPU of the box - an NCCL barrier would leave a spinning kernel on the waiting ranks' GPUs."""
+    global _cpu_group
+    if not (dist.is_available() and dist.is_initialized()):
+        return
+    if dist.get_backend() == "gloo":
+        dist.barrier(); return
+    if _cpu_group is None:
+        _cpu_group = dist.new_group(backend="gloo")
+    dist.barrier(group=_cpu_group)
+
+
 def max_over_ranks(x):
     if not (dist.is_available() and dist.is_initialized()):
         return float(x)

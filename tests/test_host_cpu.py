@@ -112,6 +112,7 @@ from popsift_b200 import dist as pdist
 rank = int(os.environ["RANK"])
 dist.init_process_group("gloo")
 pdist.barrier()
+pdist.cpu_barrier()                        # the CPU-side wait used while rank 0 alone drives all GPUs
 m = pdist.max_over_ranks(1.0 + rank)       # elapsed time: max over ranks
 s = pdist.sum_over_ranks(10 * (rank + 1))  # frames: sum over ranks
 b, e = pdist.shard(101, rank, 2)

@@ -423,7 +423,8 @@ def test_extract_banded_one_call(w, h, seed, n_ctx, seed_px, flags, exchange):
     cfg = capi.config_from_flags(flags)
     with capi.Context(cfg) as ctx:
         whole = ctx.extract(img)
-    ctxs = [capi.Context(cfg) for _ in range(n_ctx)]
+    ndev = max(1, capi.lib().psift_device_count())             # one context per GPU where the box has several
+    ctxs = [capi.Context(cfg, device=i % ndev) for i in range(n_ctx)]
     try:
         got = capi.extract_banded(ctxs, img, max_seed_pixels=seed_px)
         again = capi.extract_banded(ctxs, img, max_seed_pixels=seed_px)      # the slots are reused: no stale halo rows
