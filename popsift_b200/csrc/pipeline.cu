@@ -289,15 +289,15 @@ static int setup_pyramid_impl( psift_ctx* c, Slot& s, int w, int h, const Region
 
     if( linear_needed( c->cfg.desc_mode ) || relative ) {
         /* bilinear point-of-view of every Gaussian level (Octave::alloc_data_tex, sift_octave.cu:211-248) */
-        if( reg.kind == 1 ) return fail( PSIFT_E_INVALID, "banded extraction supports the loop and grid descriptor modes only" );
         s.lintex_h.assign( (size_t)n_oct * n_lvl, 0 );
         for( int o = L.oct_begin; o < L.oct_end; o++ )
             for( int l = 0; l < n_lvl; l++ ) {
                 cudaResourceDesc rd; memset( &rd, 0, sizeof rd );
                 rd.resType = cudaResourceTypePitch2D;
-                rd.res.pitch2D.devPtr = L.base[o] + (size_t)l * L.lstride[o];
+                /* a band binds the rows it stores; the kernels shift the sample row by row_lo (gradient_lin) */
+                rd.res.pitch2D.devPtr = L.base[o] + (size_t)l * L.lstride[o] + (size_t)L.row_lo[o] * L.pitch[o];
                 rd.res.pitch2D.desc = cudaCreateChannelDesc( 32, 0, 0, 0, cudaChannelFormatKindFloat );
-                rd.res.pitch2D.width = L.w[o]; rd.res.pitch2D.height = L.h[o];
+                rd.res.pitch2D.width = L.w[o]; rd.res.pitch2D.height = L.row_hi[o] - L.row_lo[o];
                 rd.res.pitch2D.pitchInBytes = (size_t)L.pitch[o] * sizeof(float);
                 cudaTextureDesc td; memset( &td, 0, sizeof td );
                 td.normalizedCoords = 0;

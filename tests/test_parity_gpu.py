@@ -414,6 +414,11 @@ def _canon_merged(ex):
     (512, 1280, 9, 2, 128 * 320, [], 1),                             # default Config (2x upscale), split 2, two bands
     (640, 2560, 10, 4, 320 * 1280, ["--downsampling", "0", "--mode", "vlfeat", "--desc-mode", "grid"], 1),   # split 0
     (600, 2048, 11, 2, 1, ["--downsampling", "0", "--mode", "opencv", "--gauss-mode", "opencv"], None),      # deepest split the planner allows
+    # the texture-sampling descriptor modes: a band binds its stored rows, the sample row is shifted by the band's first row
+    (768, 3072, 12, 3, 192 * 768, ["--downsampling", "0", "--desc-mode", "igrid", "--mode", "vlfeat"], 1),
+    (512, 1280, 13, 2, 128 * 320, ["--desc-mode", "notile"], 1),
+    (640, 2560, 14, 4, 320 * 1280, ["--downsampling", "0", "--desc-mode", "iloop"], 1),
+    (1024, 768, 15, 3, 128 * 96, ["--downsampling", "0", "--desc-mode", "igrid"], 0),                        # recomputed halos + textures
 ])
 def test_extract_banded_one_call(w, h, seed, n_ctx, seed_px, flags, exchange):
     """psift_extract_banded (several contexts on this GPU; on a multi-GPU box they are one per GPU and the halo and seed
