@@ -165,3 +165,24 @@ def test_demo_cli_fails_loudly_without_gpu(tmp_path):
     p = tmp_path / "a.pgm"; p.write_bytes(b"P5\n4 4\n255\n" + bytes(16))
     r = subprocess.run([exe, "-i", str(p), "--desc-mode", "grid"], capture_output=True, text=True, cwd=tmp_path)
     assert r.returncode != 0 and "no CUDA device" in r.stderr
+
+
+def test_cmake_package_installs_and_is_found(tmp_path):
+    """The drop-in's packaging (reference src/CMakeLists.txt, src/cmake/Config.cmake.in:33-43): the project installs
+    libpopsift + PopSiftConfig.cmake, and a caller that only says find_package(PopSift) / PopSift::popsift builds
+    against the installed headers and library (nvcc cross-compiles sm_100a here; nothing is run)."""
+    import shutil
+    if not shutil.which("cmake"): pytest.skip("cmake not installed")
+    b, inst, cons = tmp_path / "b", tmp_path / "inst", tmp_path / "cons"
+    def run(*cmd):
+        r = subprocess.run(list(cmd), capture_output=True, text=True, timeout=1500)
+        assert r.returncode == 0, " ".join(cmd) + "\n" + r.stdout[-1500:] + r.stderr[-1500:]
+    run("cmake", "-S", ROOT, "-B", str(b), "-DCMAKE_BUILD_TYPE=Release")
+    run("cmake", "--build", str(b), "-j8")
+    run("cmake", "--install", str(b), "--prefix", str(inst))
+    assert (inst / "lib" / "cmake" / "PopSift" / "PopSiftConfig.cmake").exists()
+    assert (inst / "include" / "popsift" / "popsift.h").exists() and (inst / "include" / "psift.h").exists()
+    assert any(f.name.startswith("libpopsift.so") for f in (inst / "lib").iterdir())
+    run("cmake", "-S", os.path.join(ROOT, "tests", "cmake_consumer"), "-B", str(cons), "-DCMAKE_PREFIX_PATH=" + str(inst))
+    run("cmake", "--build", str(cons))
+    assert (cons / "consumer").exists()
