@@ -34,6 +34,7 @@ PYR_DRAM_BYTES = 229e6         # dram read+write of the 46 pyramid launches of o
 REF_REPEATS = 3
 CXX_PRODUCERS = 2     # caller threads per GPU that enqueue() and get() in the C++-class leg
 CXX_WINDOW = 6        # jobs each of them keeps outstanding
+ONE_OBJECT_PRODUCERS = 4   # caller threads per GPU when ONE PopSift object serves all GPUs of the box
 REF_MAX_FRAMES = 2000
 
 
@@ -200,7 +201,8 @@ def tiled_leg(n_gpus, steps=8, warmup=2):
             "ms_per_image": 1e3 * t_band, "images_per_sec": 1.0 / t_band,
             "unsplit_1gpu_ms_per_image": 1e3 * t_whole, "speedup_vs_unsplit": t_whole / t_band,
             "unsplit_stage_ms": {k: round(v, 3) for k, v in stage.items()},
-            "keypoints": whole.n_feat, "descriptors": whole.n_desc, "equal_to_unsplit": bool(same), "steps": steps, "timing": "wall clock"}
+            "keypoints": whole.n_feat, "descriptors": whole.n_desc, "equal_to_unsplit": bool(same), "steps": steps, "timing": "wall clock",
+            "host": {"cpus_allowed": len(os.sched_getaffinity(0)), "loadavg": os.getloadavg()[0]}}
 
 
 def bench_tiled(args, rank, world):
@@ -284,13 +286,36 @@ def main():
     from popsift_b200 import dist as pdist
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the extraction path has no CPU fallback")
+    imgs = frames()
+
+    # The two legs in which ONE process drives every GPU of the box run first, while the other ranks wait on a CPU-side
+    # (gloo) barrier and have not created a CUDA context yet: a GPU shared with another process's live context moved
+    # rank 0's result downloads at 1.3 GB/s on the 8-GPU box (143 ms for a 16384^2 frame's results instead of 2 ms).
+    if world > 1:
+        dist.init_process_group("gloo")                      # CPU only; the NCCL group for the per-rank legs follows
+    one_object, tiled = None, None
+    if rank == 0:
+        if world > 1:
+            # ONE PopSift object over all N GPUs of the box (its in-process dispatcher: one worker per GPU, shared queue)
+            n_prod = max(2, min(ONE_OBJECT_PRODUCERS * world, (os.cpu_count() or 8) - world))   # caller threads; each worker needs a core too
+            r1 = capi.cxx_stream(imgs, args.warmup * BATCH * world, args.steps * BATCH * world, first_device=0, n_devices=world,
+                                 n_producers=n_prod, window=CXX_WINDOW)
+            one_object = {"value": r1["images_per_sec"], "unit": "images/s", "devices": r1["devices"], "producer_threads": n_prod,
+                          "what": "one PopSift object dispatching to all GPUs of this process (rank 0, before the other ranks start), wall clock"}
+        if not args.no_tiled:
+            try:
+                tiled = tiled_leg(world)                     # BASELINE config 5: one giant image over the GPUs of the box
+            except Exception as e:                           # the headline line must not depend on this leg
+                tiled = {"error": repr(e)[:300]}
+    if world > 1:
+        dist.barrier()                                       # gloo: the waiting ranks sleep on a socket
+
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        pdist.use_group(dist.new_group(backend="nccl", device_id=torch.device("cuda", local)))   # barrier + max-over-ranks of the timed legs
 
     barrier = pdist.barrier
 
-    imgs = frames()
     dev_imgs = [torch.from_numpy(im).cuda() for im in imgs]
     ctx = capi.Context(capi.default_config(), device=local)
     sub_dev = lambda t: ctx.submit_dev_u8(t.data_ptr(), W, H, W)
@@ -334,18 +359,6 @@ def main():
     barrier()
     dt_cxx = pdist.max_over_ranks(cxx["seconds"])
     cxx_feat = pdist.sum_over_ranks(cxx["n_feat"]) / world; cxx_desc = pdist.sum_over_ranks(cxx["n_desc"]) / world
-    # ONE PopSift object over all N GPUs of the box (its in-process dispatcher: one worker per GPU, shared queue), driven
-    # from rank 0 while the other ranks wait
-    one_object = None
-    if world > 1:
-        torch.cuda.synchronize(); pdist.cpu_barrier()        # the other ranks wait on the CPU: their GPUs must be idle
-        if rank == 0:
-            r1 = capi.cxx_stream(imgs, args.warmup * BATCH * world, n_frames * world, first_device=0, n_devices=world,
-                                 n_producers=CXX_PRODUCERS * world, window=CXX_WINDOW)
-            one_object = {"value": r1["images_per_sec"], "unit": "images/s", "devices": r1["devices"], "producer_threads": CXX_PRODUCERS * world,
-                          "what": "one PopSift object dispatching to all GPUs of this process (rank 0; the other ranks idle), wall clock"}
-        pdist.cpu_barrier()
-
     # kernel-stage times (CUDA events on the frame's stream), one frame at a time, warm
     stage = {}
     for i in range(8):
@@ -406,17 +419,6 @@ def main():
                     "traffic": BLUR_DRAM_BYTES, "launch_ms": dom_ms, "launch_ms_stream_full": dom_ms_busy,
                     "per_level_ms": [float(x) for x in lv_alone], "per_level_ms_stream_full": [float(x) for x in lv], "per_level_bytes": lvl_bytes,
                     "timing": "CUDA events on the stream each launch goes to (psift_debug_time_levels), frames one at a time; *_stream_full: all frame slots busy"}}
-
-    # BASELINE config 5 (one giant image over the GPUs of the box), driven from rank 0 while the other ranks wait
-    tiled = None
-    if not args.no_tiled:
-        torch.cuda.synchronize(); pdist.cpu_barrier()
-        if rank == 0:
-            try:
-                tiled = tiled_leg(world)
-            except Exception as e:                  # the headline line must not depend on this leg
-                tiled = {"error": repr(e)[:300]}
-        pdist.cpu_barrier()
 
     if rank == 0:
         line = {"metric": "images_per_sec_1080p", "value": world * n_frames / dt_dev, "unit": "images/s", "n_gpus": world,

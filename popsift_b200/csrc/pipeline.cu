@@ -407,8 +407,10 @@ struct ResultPool {
     {
         {
             std::lock_guard<std::mutex> lk( mu );
+            size_t best = idle.size();                     /* best fit: a frame must not walk off with a giant image's block */
             for( size_t i = 0; i < idle.size(); i++ )
-                if( idle[i]->ext_cap >= n_ext && idle[i]->desc_cap >= n_desc ) { psift_result_block* b = idle[i]; idle[i] = idle.back(); idle.pop_back(); return b; }
+                if( idle[i]->ext_cap >= n_ext && idle[i]->desc_cap >= n_desc && ( best == idle.size() || idle[i]->desc_cap < idle[best]->desc_cap ) ) best = i;
+            if( best < idle.size() ) { psift_result_block* b = idle[best]; idle[best] = idle.back(); idle.pop_back(); return b; }
         }
         psift_result_block* b = new( std::nothrow ) psift_result_block();
         if( !b ) return nullptr;
@@ -435,11 +437,20 @@ struct ResultPool {
     void put( psift_result_block* b )
     {
         if( !b ) return;
+        psift_result_block* victim = nullptr;
         {
             std::lock_guard<std::mutex> lk( mu );
-            if( idle.size() < 64 ) { idle.push_back( b ); return; }
+            idle.push_back( b );
+            if( idle.size() > 64 ) {
+                /* full: the SMALLEST block goes (64 frame-sized blocks left behind by a stream must not push out the one
+                 * block of a giant image, which costs 100 ms to page-lock again) */
+                size_t k = 0;
+                for( size_t i = 1; i < idle.size(); i++ )
+                    if( (long long)idle[i]->desc_cap * 512 + (long long)idle[i]->ext_cap * 96 < (long long)idle[k]->desc_cap * 512 + (long long)idle[k]->ext_cap * 96 ) k = i;
+                victim = idle[k]; idle[k] = idle.back(); idle.pop_back();
+            }
         }
-        destroy( b );
+        destroy( victim );
     }
 };
 ResultPool& result_pool() { static ResultPool* p = new ResultPool; return *p; }    /* never torn down: results may outlive every context */

@@ -16,13 +16,29 @@ def shard(n_items, rank, world):
     return begin, begin + base + (1 if rank < rem else 0)
 
 
+_group = None          # the group barrier() / max_over_ranks() / sum_over_ranks() run on (None: the default group)
+
+
+def use_group(group):
+    """bench.py starts on a gloo default group (CPU-only waits) and switches its timing plumbing to an NCCL group here"""
+    global _group
+    _group = group
+
+
+def _backend():
+    return dist.get_backend(_group) if _group is not None else dist.get_backend()
+
+
 def _device():
-    return torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    return torch.device("cuda", torch.cuda.current_device()) if _backend() == "nccl" else torch.device("cpu")
 
 
 def barrier():
     if dist.is_available() and dist.is_initialized():
-        dist.barrier()
+        if _backend() == "nccl":
+            dist.barrier(group=_group, device_ids=[torch.cuda.current_device()])
+        else:
+            dist.barrier(group=_group)
     if torch.cuda.is_available():
         torch.cuda.synchronize()
 
@@ -47,7 +63,7 @@ def max_over_ranks(x):
     if not (dist.is_available() and dist.is_initialized()):
         return float(x)
     t = torch.tensor([float(x)], dtype=torch.float64, device=_device())
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=_group)
     return float(t.item())
 
 
@@ -55,5 +71,5 @@ def sum_over_ranks(x):
     if not (dist.is_available() and dist.is_initialized()):
         return float(x)
     t = torch.tensor([float(x)], dtype=torch.float64, device=_device())
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=_group)
     return float(t.item())
