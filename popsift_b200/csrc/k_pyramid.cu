@@ -938,8 +938,6 @@ static cudaError_t launch_pyramid_relative( const PyrLayout& L, cudaTextureObjec
 
 /* Build every Gaussian level of every octave (reference Pyramid::build_pyramid,
  * s_pyramid_build.cu:460-596, default branch :549-577). */
-static int cluster_first_octave( const PyrLayout& L, const GaussTables& T, int* band_max, int* wp_max, size_t* smem );
-static cudaError_t launch_cluster( const PyrLayout& L, const GaussTables& T, int o_first, int band_max, int wp_max, size_t smem, cudaStream_t st );
 
 /* ------------------------------------------------------------------------------------------ */
 /* Fixed9 / Fixed15 (reference s_pyramid_fixed.cu, K8): every level is filtered in ONE step from a fixed source
@@ -1103,15 +1101,7 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
     const bool fork = S.side[0] != nullptr;
     bool side_used[2] = { false, false };
     cudaError_t e;
-    /* the deep octaves (a few ten thousand pixels and less) are built by ONE cluster launch on the chain stream */
-    int cl_band = 0, cl_wp = 0; size_t cl_smem = 0;
-    const int cl_first = direct_scaling ? 0 : cluster_first_octave( L, T, &cl_band, &cl_wp, &cl_smem );
     for( int o = L.oct_begin; o < L.oct_end; o++ ) {
-        if( cl_first > 0 && o == cl_first ) {
-            if( ( e = launch_cluster( L, T, o, cl_band, cl_wp, cl_smem, S.chain ) ) != cudaSuccess ) return e;
-            if( launches ) ++*launches;
-            break;
-        }
         /* level 0 of octave 0 comes from the input image, of any other octave from the previous
          * octave's fused downscale (or, for the first octave of a seeded pass, from the caller) */
         for( int l = ( o == 0 || direct_scaling ? 0 : 1 ); l < L.n_lvl; l++ ) {
@@ -1138,258 +1128,6 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
             if( ( e = cudaStreamWaitEvent( S.chain, S.side_done[k], 0 ) ) != cudaSuccess ) return e;
         }
     return cudaSuccess;
-}
-
-/* ------------------------------------------------------------------------------------------
- * The deep octaves in ONE launch: a thread-block cluster keeps the planes in distributed shared memory.
- *
- * From the octave on whose planes have a few ten thousand pixels, a Gaussian level is microseconds of arithmetic but
- * costs a launch of its own (5-7 us each with programmatic dependent launch; 25 of them form a dependency chain of
- * about 90 us per 1080p frame).  Here a cluster of CL_NC blocks builds ALL levels of ALL remaining octaves: block k owns a
- * band of rows of the octave; the source level S and the horizontal results I of the band live in its shared memory; the
- * vertical pass reads the rows it lacks from the two neighbouring blocks' I through distributed shared memory; a cluster
- * barrier per level replaces the launch boundary.  Every level still goes to global memory (the later stages read it),
- * and the pick-every-second downscale that seeds the next octave is written from the same registers; the next octave's
- * bands are then loaded back from that seed plane (L2).  Octaves too small to give every block HALO_MIN rows use fewer
- * blocks; the others only keep the barrier.
- * Same arithmetic in the same order as k_blur2 (s_pyramid_build_aa.cu:29-49, 71-86): planes stay bit-identical.
- * ------------------------------------------------------------------------------------------ */
-} // namespace psift
-#include <cooperative_groups.h>
-namespace psift {
-namespace cg = cooperative_groups;
-
-constexpr int CL_NC   = 8;        /* blocks per cluster (the portable maximum) */
-constexpr int CL_NT   = 512;
-constexpr int CL_PAD  = 16;       /* replicated columns left and right of a source row: the horizontal pass needs no clamps */
-constexpr int CL_HMAX = 16;       /* largest supported span - 1 */
-constexpr int CL_RV   = 4;        /* rows per thread in the vertical pass */
-constexpr int CL_BMAX = 64;       /* most rows of a band */
-
-struct ClusterArgs {
-    PyrLayout L;
-    int   o_first;                /* first octave built here; its level 0 is in global memory already */
-    int   band_max, wp_max;       /* shared-memory sizing: rows per band, padded width (floats) of octave o_first */
-    Taps  inc[MAX_LVL];
-};
-
-/* bands of an octave of h rows: B rows each, n of them (the last one what is left) */
-__host__ __device__ inline void cl_bands( int h, int& n, int& B )
-{
-    B = ( h + CL_NC - 1 ) / CL_NC;
-    n = ( h + B - 1 ) / B;
-}
-
-/* Both passes take the tap count at run time and keep the code SMALL (a few hundred instructions for the whole kernel):
- * one block per SM executes every level's code only a handful of times, so unrolled per-tap-count variants (as in the
- * tile kernels) made this kernel instruction-fetch-bound - 4.5 us per level whatever the plane size, slower than the
- * launches it replaces.  A thread owns 4 adjacent outputs; the 4 values it needs on either side at tap `off` are the ones
- * of tap `off + 1` shifted by one, so a tap costs one new load per side and the accumulation order is the reference's. */
-__device__ __noinline__ void cl_hpass( int H, const float* __restrict__ S, float* __restrict__ I, int rows, int w, int sp, int ip, const float* g )
-{
-    const int ngrp = ( w + 3 ) >> 2;
-    for( int it = threadIdx.x; it < rows * ngrp; it += CL_NT ) {
-        const int r = it / ngrp, x = ( it - r * ngrp ) * 4;
-        const float* c = S + r * sp + CL_PAD + x;                /* c[j]: the source pixel of output j */
-        float l0 = c[-H], l1 = c[1 - H], l2 = c[2 - H], l3 = c[3 - H];
-        float r0 = c[H],  r1 = c[1 + H], r2 = c[2 + H], r3 = c[3 + H];
-        const float g0 = g[0];
-        float o0 = __fmaf_rn( c[0], g0, 0.0f ), o1 = __fmaf_rn( c[1], g0, 0.0f ), o2 = __fmaf_rn( c[2], g0, 0.0f ), o3 = __fmaf_rn( c[3], g0, 0.0f );
-        for( int off = H; off > 0; off-- ) {
-            const float gg = g[off];
-            o0 = __fmaf_rn( __fadd_rn( l0, r0 ), gg, o0 ); o1 = __fmaf_rn( __fadd_rn( l1, r1 ), gg, o1 );
-            o2 = __fmaf_rn( __fadd_rn( l2, r2 ), gg, o2 ); o3 = __fmaf_rn( __fadd_rn( l3, r3 ), gg, o3 );
-            /* tap off - 1: left values move one to the right, right values one to the left */
-            l0 = l1; l1 = l2; l2 = l3; l3 = c[4 - off];
-            r3 = r2; r2 = r1; r1 = r0; r0 = c[off - 1];
-        }
-        *reinterpret_cast<float4*>( I + r * ip + x ) = make_float4( o0, o1, o2, o3 );
-    }
-}
-
-/* rows the band lacks: from the blocks that own them into the halo rows of my buffer.  All loads are independent, so the
- * distributed-shared-memory latency (a few hundred cycles) is paid once, not once per tap as when the vertical pass itself
- * read the remote rows (that made a level of the tiniest octave cost 2.7 us).  rowp[k]: where row lo - CL_HMAX + k lives. */
-__device__ __forceinline__ void cl_fetch_halo( int H, const float* const* rowp, float* Iext, int rows, int w, int ip )
-{
-    const int ngrp = ( w + 3 ) >> 2;
-    for( int it = threadIdx.x; it < 2 * H * ngrp; it += CL_NT ) {
-        const int hr = it / ngrp, x = ( it - hr * ngrp ) * 4;
-        const int k = hr < H ? CL_HMAX - H + hr : CL_HMAX + rows + ( hr - H );
-        *reinterpret_cast<float4*>( Iext + k * ip + x ) = *reinterpret_cast<const float4*>( rowp[k] + x );
-    }
-}
-
-/* Iext: rows lo - CL_HMAX .. hi + CL_HMAX of the horizontal results (mine in the middle, the halo fetched), local */
-__device__ __noinline__ void cl_vpass( int H, const float* __restrict__ Iext, float* __restrict__ S, float* __restrict__ dst, float* __restrict__ ds,
-                                       int lo, int hi, int w, int sp, int ip, int pitch, int ds_pitch, const float* g )
-{
-    const int rows = hi - lo, nrg = ( rows + CL_RV - 1 ) / CL_RV;
-    for( int it = threadIdx.x; it < nrg * w; it += CL_NT ) {
-        const int rg = it / w, x = it - rg * w;
-        const float* q = Iext + ( CL_HMAX + rg * CL_RV ) * ip + x;   /* q[j * ip]: horizontal result of output row j */
-        float u0 = q[-H * ip], u1 = q[( 1 - H ) * ip], u2 = q[( 2 - H ) * ip], u3 = q[( 3 - H ) * ip];
-        float d0 = q[H * ip],  d1 = q[( 1 + H ) * ip], d2 = q[( 2 + H ) * ip], d3 = q[( 3 + H ) * ip];
-        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
-        for( int off = H; off > 0; off-- ) {
-            const float gg = g[off];
-            a0 = __fmaf_rn( u0, gg, a0 ); a1 = __fmaf_rn( u1, gg, a1 ); a2 = __fmaf_rn( u2, gg, a2 ); a3 = __fmaf_rn( u3, gg, a3 );
-            a0 = __fmaf_rn( d0, gg, a0 ); a1 = __fmaf_rn( d1, gg, a1 ); a2 = __fmaf_rn( d2, gg, a2 ); a3 = __fmaf_rn( d3, gg, a3 );
-            u0 = u1; u1 = u2; u2 = u3; u3 = q[( 4 - off ) * ip];
-            d3 = d2; d2 = d1; d1 = d0; d0 = q[( off - 1 ) * ip];
-        }
-        /* after the last tap u_j = row j: the centre */
-        const float g0 = g[0];
-        const float v[CL_RV] = { __fmaf_rn( u0, g0, a0 ), __fmaf_rn( u1, g0, a1 ), __fmaf_rn( u2, g0, a2 ), __fmaf_rn( u3, g0, a3 ) };
-        #pragma unroll
-        for( int j = 0; j < CL_RV; j++ ) {
-            const int r = lo + rg * CL_RV + j;
-            if( r < hi ) {
-                dst[(size_t)r * pitch + x] = v[j];                   /* the level: to global memory ... */
-                S[( r - lo ) * sp + CL_PAD + x] = v[j];              /* ... and, as the next level's source, back into S */
-                if( ds && !( ( r | x ) & 1 ) ) ds[(size_t)( r >> 1 ) * ds_pitch + ( x >> 1 )] = v[j];
-            }
-        }
-    }
-}
-
-/* replicate the edge columns of the band's source rows into the pads (columns >= w inside the last float4 included) */
-__device__ __forceinline__ void cl_fill_pads( float* S, int rows, int w, int sp )
-{
-    const int wp = ( w + 3 ) & ~3;
-    const int nright = CL_PAD + ( wp - w );
-    for( int it = threadIdx.x; it < rows * ( CL_PAD + nright ); it += CL_NT ) {
-        const int r = it / ( CL_PAD + nright ), k = it - r * ( CL_PAD + nright );
-        float* row = S + r * sp + CL_PAD;
-        if( k < CL_PAD ) row[-1 - k] = row[0];
-        else             row[w + ( k - CL_PAD )] = row[w - 1];
-    }
-}
-
-/* The barrier between the horizontal and the vertical pass of a level only has to make SHARED memory visible across the
- * cluster (the others read my horizontal results through distributed shared memory): a block-scope fence (my
- * shared-memory writes are performed; the memory a neighbour reads is physically this SM's) and a RELAXED arrive.
- * Global visibility (the seed plane of the next octave) comes from the full release/acquire barrier at the end of
- * every octave.  (Measured: the barrier flavour is not what the kernel's time depends on.) */
-__device__ __forceinline__ void cl_sync_shared()
-{
-    __threadfence_block();
-    asm volatile( "barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory" );
-}
-
-__device__ __forceinline__ void cl_level( int H, float* S, float* Iext, const float* const* rowp, float* dst, float* ds,
-                                          int lo, int hi, int w, int sp, int ip, int pitch, int ds_pitch, const float* g, bool active )
-{
-    if( active ) cl_hpass( H, S, Iext + CL_HMAX * ip, hi - lo, w, sp, ip, g );
-    __syncthreads();
-    cl_sync_shared();                                           /* every band's horizontal results are complete */
-    if( active ) {
-        cl_fetch_halo( H, rowp, Iext, hi - lo, w, ip );
-        __syncthreads();
-        cl_vpass( H, Iext, S, dst, ds, lo, hi, w, sp, ip, pitch, ds_pitch, g );
-        __syncthreads();
-        cl_fill_pads( S, hi - lo, w, sp );
-    }
-    __syncthreads();
-}
-
-__global__ void __launch_bounds__( CL_NT, 1 )
-k_pyr_cluster( const __grid_constant__ ClusterArgs a )
-{
-    extern __shared__ __align__( 16 ) float cl_smem[];
-    __shared__ float taps[CL_HMAX + 1];
-    __shared__ const float* rowp[CL_BMAX + CL_RV + 2 * CL_HMAX];
-    cg::cluster_group cluster = cg::this_cluster();
-    const int rank = (int)cluster.block_rank();
-    const PyrLayout& L = a.L;
-    const int sp_max = a.wp_max + 2 * CL_PAD;
-    float* S  = cl_smem;                                        /* [band][wp + 2 pads]  source level, then the level just built */
-    float* I0 = S + a.band_max * sp_max;                        /* [halo + band + halo][wp]  horizontal results, double-buffered: */
-    float* I1 = I0 + ( a.band_max + 2 * CL_HMAX ) * a.wp_max;   /*                           the others still read the previous one */
-    pdl_enter();
-    const int ds_level = L.n_lvl - 3;
-    int parity = 0;
-    for( int o = a.o_first; o < L.n_oct; o++ ) {
-        const int w = L.w[o], h = L.h[o], pitch = L.pitch[o];
-        const int wp = ( w + 3 ) & ~3, sp = wp + 2 * CL_PAD, ip = wp;
-        int n, B;
-        cl_bands( h, n, B );
-        const bool active = rank < n;
-        const int lo = min( h, rank * B ), hi = min( h, lo + B );
-        if( active ) {
-            /* level 0 of the octave: written by the previous launch (first octave) or by this cluster's downscale */
-            const float* src = L.base[o];
-            const int ngrp = wp >> 2;
-            for( int it = threadIdx.x; it < ( hi - lo ) * ngrp; it += CL_NT ) {
-                const int r = it / ngrp, x = ( it - r * ngrp ) * 4;
-                *reinterpret_cast<float4*>( S + r * sp + CL_PAD + x ) = __ldcg( reinterpret_cast<const float4*>( src + (size_t)( lo + r ) * pitch + x ) );
-            }
-            __syncthreads();
-            cl_fill_pads( S, hi - lo, w, sp );
-        }
-        __syncthreads();
-        for( int l = 1; l < L.n_lvl; l++ ) {
-            const int H = a.inc[l].span - 1;
-            float* Icur = parity ? I1 : I0;
-            parity ^= 1;
-            if( threadIdx.x <= CL_HMAX ) taps[threadIdx.x] = a.inc[l].g[threadIdx.x];
-            /* where the rows around my band live: row gr belongs to block gr / B */
-            if( active && threadIdx.x < ( hi - lo ) + CL_RV + 2 * CL_HMAX ) {
-                const int gr = min( max( lo - CL_HMAX + (int)threadIdx.x, 0 ), h - 1 );
-                const int owner = gr / B;
-                rowp[threadIdx.x] = cluster.map_shared_rank( Icur, owner ) + ( CL_HMAX + gr - owner * B ) * ip;
-            }
-            __syncthreads();
-            float* dst = L.base[o] + (size_t)l * L.lstride[o];
-            float* ds  = ( l == ds_level && o + 1 < L.n_oct ) ? L.base[o + 1] : nullptr;
-            const int dsp = ds ? L.pitch[o + 1] : 0;
-            cl_level( H, S, Icur, rowp, dst, ds, lo, hi, w, sp, ip, pitch, dsp, taps, active );
-        }
-        cluster.sync();                                         /* the seed plane of the next octave is complete and visible */
-    }
-}
-
-/* first octave the cluster kernel can take (0: none): whole planes only, supported spans, small enough planes */
-static int cluster_first_octave( const PyrLayout& L, const GaussTables& T, int* band_max, int* wp_max, size_t* smem )
-{
-    static int enabled = -1, max_px = 0;
-    if( enabled < 0 ) { enabled = env_int( "PSIFT_CLUSTER", 1 ); max_px = env_int( "PSIFT_CLUSTER_MAX_PX", 12000 ); }
-    if( !enabled || L.oct_begin != 0 || L.oct_end != L.n_oct ) return 0;
-    for( int l = 1; l < L.n_lvl; l++ ) if( T.inc[l].span - 1 > CL_HMAX || T.inc[l].span < 2 ) return 0;
-    for( int o = 1; o < L.n_oct; o++ ) {
-        if( (long)L.w[o] * L.h[o] > max_px ) continue;
-        int n, B; cl_bands( L.h[o], n, B );
-        const int wp = ( L.w[o] + 3 ) & ~3;
-        const size_t need = sizeof(float) * ( (size_t)B * ( wp + 2 * CL_PAD ) + 2 * (size_t)( B + 2 * CL_HMAX ) * wp );
-        if( need > 200 * 1024 || B > CL_BMAX ) continue;
-        if( L.n_oct - o < 2 ) return 0;                         /* a single octave: the ordinary launches do as well */
-        *band_max = B; *wp_max = wp; *smem = need;
-        return o;
-    }
-    return 0;
-}
-
-static cudaError_t launch_cluster( const PyrLayout& L, const GaussTables& T, int o_first, int band_max, int wp_max, size_t smem, cudaStream_t st )
-{
-    static bool attr_done[16] = { false };
-    int dev = 0; cudaGetDevice( &dev );
-    if( dev >= 16 || !attr_done[dev] ) {
-        cudaError_t e = cudaFuncSetAttribute( k_pyr_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 );
-        if( e != cudaSuccess ) return e;
-        if( dev < 16 ) attr_done[dev] = true;
-    }
-    ClusterArgs a;
-    a.L = L; a.o_first = o_first; a.band_max = band_max; a.wp_max = wp_max;
-    for( int l = 0; l < MAX_LVL; l++ ) a.inc[l] = T.inc[l];
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3( CL_NC ); cfg.blockDim = dim3( CL_NT ); cfg.dynamicSmemBytes = smem; cfg.stream = st;
-    cudaLaunchAttribute attr[2];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CL_NC; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[1].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    return cudaLaunchKernelEx( &cfg, k_pyr_cluster, a );
 }
 
 } // namespace psift
