@@ -17,7 +17,6 @@
 #include "common.h"
 #include "kernels.h"
 #include <algorithm>
-#include <cstdlib>
 
 namespace psift {
 
@@ -190,13 +189,14 @@ struct ExtGrid {
     int tiles_x[MAX_OCT];
 };
 
-constexpr int EX_TX = 64, EX_NT = 256;     /* tile width; the tile height TY (16 or 32 rows) is a template parameter */
+constexpr int EX_TX = 64, EX_TY = 16, EX_NT = 256;
 constexpr int EX_SW = EX_TX + 8;           /* DoG tile row: tile column x sits at x+4, so that rows load and read as float4 */
+constexpr int EX_SH = EX_TY + 2;
 
-static size_t extrema_smem( int n_lvl, int ty )
+static size_t extrema_smem( int n_lvl )
 {
-    return sizeof(float) * (size_t)( n_lvl - 1 ) * ( ty + 2 ) * EX_SW             /* DoG tile            */
-         + sizeof(unsigned short) * 2 * (size_t)( n_lvl - 3 ) * EX_TX * ty;       /* two survivor queues */
+    return sizeof(float) * (size_t)( n_lvl - 1 ) * EX_SH * EX_SW                  /* DoG tile            */
+         + sizeof(unsigned short) * 2 * (size_t)( n_lvl - 3 ) * EX_TX * EX_TY;    /* two survivor queues */
 }
 
 /* One block = one 64x16 tile of one octave, all levels.
@@ -207,12 +207,11 @@ static size_t extrema_smem( int n_lvl, int ty )
  *             L2-resident Gaussian planes, since the iteration may walk out of the tile)
  * NLVL > 0 fixes the number of Gaussian levels at compile time (all loads of a pixel in flight
  * together); NLVL == 0 takes it from the layout. */
-template<int MODE, int NLVL, int TY>
+template<int MODE, int NLVL>
 __global__ void __launch_bounds__( EX_NT )
 k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid G, const __grid_constant__ Consts K,
            Cand* cand, int cand_stride, Counters* ct )
 {
-    constexpr int EX_TY = TY, EX_SH = TY + 2;
     extern __shared__ __align__( 16 ) float ex_smem[];
     __shared__ int n1, n2;
     pdl_enter();
@@ -270,8 +269,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
 
     /* ---- phase 1: first contrast test, four voxels per thread and level ---- */
     {
-        const int g = tid % ( EX_TX / 4 );                                /* 16 x 16 threads = 64 x 16 pixels per pass */
-        for( int y = tid / ( EX_TX / 4 ); y < EX_TY; y += EX_NT / ( EX_TX / 4 ) ) {
+        const int g = tid % ( EX_TX / 4 ), y = tid / ( EX_TX / 4 );       /* 16 x 16 threads = 64 x 16 pixels */
         const int gy = ty0 + y;
         unsigned inside = 0;
         #pragma unroll
@@ -292,10 +290,9 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
                     int pos = atomicAdd( &n1, __popc( m ) );
                     #pragma unroll
                     for( int j = 0; j < 4; j++ )
-                        if( m & ( 1u << j ) ) q1[pos++] = (unsigned short)( ( 4 * g + j ) | ( y << 6 ) | ( level << 11 ) );
+                        if( m & ( 1u << j ) ) q1[pos++] = (unsigned short)( ( 4 * g + j ) | ( y << 6 ) | ( level << 10 ) );
                 }
             }
-        }
     }
     __syncthreads();
 
@@ -303,7 +300,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     const int cnt1 = n1;
     for( int i = tid; i < cnt1; i += EX_NT ) {
         const unsigned e = q1[i];
-        const int x = e & 63, y = ( e >> 6 ) & 31, level = e >> 11;
+        const int x = e & 63, y = ( e >> 6 ) & 15, level = e >> 10;
         const float* c = D + ( level * EX_SH + y + 1 ) * EX_SW + x + 4;
         const float v = *c;
         bool gt = true, lt = true;
@@ -336,7 +333,7 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     const float h_div = __fdiv_rn( (float)h, (float)K.grid_size );
     for( int i = tid; i < cnt2; i += EX_NT ) {
         const unsigned e = q2[i];
-        const int x = tx0 + ( e & 63 ), y = ty0 + ( ( e >> 6 ) & 31 ), level = e >> 11;
+        const int x = tx0 + ( e & 63 ), y = ty0 + ( ( e >> 6 ) & 15 ), level = e >> 10;
         const float val = D[( level * EX_SH + ( y - ty0 ) + 1 ) * EX_SW + ( x - tx0 ) + 4];
         Cand c;
         if( refine_extremum<MODE>( dv, K, x, y, level, val, w_div, h_div, c ) ) {
@@ -457,26 +454,9 @@ k_sort_rank( const Cand* grouped, const Counters* ct, const SortScratch* ss, con
     }
 }
 
-/* dynamic shared memory above 48 KB has to be allowed once per kernel and device (not inside a stream capture: the first
- * frame of a slot always runs as plain launches) */
-template<int MODE, int NL, int TY>
-static cudaError_t extrema_allow_smem( size_t smem )
-{
-    static size_t allowed[16] = { 0 };
-    int dev = 0; cudaGetDevice( &dev );
-    if( dev >= 0 && dev < 16 && allowed[dev] >= smem ) return cudaSuccess;
-    const cudaError_t e = cudaFuncSetAttribute( k_extrema<MODE, NL, TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem );
-    if( e == cudaSuccess && dev >= 0 && dev < 16 ) allowed[dev] = smem;
-    return e;
-}
-
 cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted, Cand* sort_tmp,
                             int ext_capacity, Counters* ct, SortScratch* ss, cudaStream_t st, long long* launches )
 {
-    /* tile height: 16 rows, or 32 (half the blocks, 6 % instead of 12.5 % halo rows, 74 KB of shared memory) */
-    static int ty_rows = 0;
-    if( !ty_rows ) { const char* e = getenv( "PSIFT_EXT_TY" ); ty_rows = ( e && atoi( e ) == 32 ) ? 32 : 16; }
-    const int EX_TY = ty_rows;
     ExtGrid G;
     int nb = 0;
     for( int o = 0; o < L.n_oct; o++ ) {
@@ -488,18 +468,16 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     }
     for( int o = L.n_oct; o <= MAX_OCT; o++ ) G.first_block[o] = nb;
     if( nb == 0 ) return cudaErrorInvalidValue;
-    const size_t smem = extrema_smem( L.n_lvl, EX_TY );
-    if( L.n_lvl > 30 ) return cudaErrorInvalidValue;                      /* queue entries hold 5 bits of level */
-#define PSIFT_EXT_LAUNCH_T( MODE, NL, TY )                                                                    \
+    const size_t smem = extrema_smem( L.n_lvl );
+    if( L.n_lvl > 60 ) return cudaErrorInvalidValue;                      /* queue entries hold 6 bits of level */
+#define PSIFT_EXT_LAUNCH( MODE )                                                                             \
     do {                                                                                                      \
-        cudaError_t e = extrema_allow_smem<MODE, NL, TY>( smem );                                             \
-        if( e != cudaSuccess ) return e;                                                                      \
-        launch_pdl( k_extrema<MODE, NL, TY>, dim3( nb ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct ); \
-    } while( 0 )
-#define PSIFT_EXT_LAUNCH( MODE )                                                                              \
-    do {                                                                                                      \
-        if( L.n_lvl == 6 ) { if( EX_TY == 32 ) PSIFT_EXT_LAUNCH_T( MODE, 6, 32 ); else PSIFT_EXT_LAUNCH_T( MODE, 6, 16 ); } \
-        else               { if( EX_TY == 32 ) PSIFT_EXT_LAUNCH_T( MODE, 0, 32 ); else PSIFT_EXT_LAUNCH_T( MODE, 0, 16 ); } \
+        if( L.n_lvl == 6 ) launch_pdl( k_extrema<MODE, 6>, dim3( nb ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct ); \
+        else {                                                                                                \
+            cudaError_t e = cudaFuncSetAttribute( k_extrema<MODE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem ); \
+            if( e != cudaSuccess ) return e;                                                                  \
+            launch_pdl( k_extrema<MODE, 0>, dim3( nb ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct );       \
+        }                                                                                                     \
     } while( 0 )
     switch( K.sift_mode ) {
     case PSIFT_MODE_OPENCV: PSIFT_EXT_LAUNCH( PSIFT_MODE_OPENCV ); break;
@@ -507,7 +485,6 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     default:                PSIFT_EXT_LAUNCH( PSIFT_MODE_POPSIFT ); break;
     }
 #undef PSIFT_EXT_LAUNCH
-#undef PSIFT_EXT_LAUNCH_T
     launch_pdl( k_extrema_finish, dim3( 1 ), dim3( 32 ), 0, st, ct, L.n_oct, K.max_extrema, ext_capacity );
     /* order the candidates (ss was zeroed together with the counters at the start of the frame) */
     SortShifts sh;
