@@ -120,6 +120,31 @@ def test_device_resident_input_equals_host_input():
     assert a.feat.tobytes() == c.feat.tobytes() and a.desc.tobytes() == c.desc.tobytes()
 
 
+def test_wait_take_results_outlive_job_and_context():
+    """psift_wait_take: the caller takes the job's page-locked result block; its arrays stay valid after psift_job_free
+    and after the context is gone, until psift_result_block_free; the slot goes on with another block."""
+    import ctypes as C
+    L = capi.lib()
+    img = load("g640")
+    with capi.Context(capi.default_config()) as ctx:
+        want = ctx.extract(img)
+        taken = []
+        for _ in range(3):                                   # the same slot each time: it must pick up a fresh block
+            job = ctx.submit(img)
+            r = capi.Result(); blk = C.c_void_p()
+            assert L.psift_wait_take(job, C.byref(r), C.byref(blk)) == 0, L.psift_last_error()
+            r2 = capi.Result()
+            assert L.psift_wait(job, C.byref(r2)) != 0       # taken: the job has nothing left to hand out
+            ctx.free(job)
+            taken.append((r, blk))
+        again = ctx.extract(img)                             # the ordinary path still works on that slot
+        assert again.desc.tobytes() == want.desc.tobytes()
+    for r, blk in taken:                                     # context destroyed: the blocks are still ours
+        got = capi.Extraction(r)
+        assert got.n_feat == want.n_feat and got.feat.tobytes() == want.feat.tobytes() and got.desc.tobytes() == want.desc.tobytes()
+        L.psift_result_block_free(blk)
+
+
 def test_reconfigure_and_resize():
     with capi.Context(capi.default_config()) as ctx:
         a = ctx.extract(load("g256"))
