@@ -58,7 +58,7 @@ typedef struct psift_config {
     int   filter_sorting;       /* PSIFT_FILTER_* */
     int   assume_initial_blur;  /* 1 */
     float initial_blur;         /* 0.5 */
-    int   deterministic_order;  /* 1: features come back sorted (octave, level, y, x) -- an extension;
+    int   deterministic_order;  /* 1 (default): features come back sorted (octave, level, y, x) -- an extension;
                                    the reference's order is whatever its atomics produced */
     int   scaling_mode;         /* 0: every octave is seeded by the previous one (Config::ScaleDefault);
                                    1: level 0 of EVERY octave is filtered straight from the input image

@@ -454,6 +454,17 @@ k_sort_rank( const Cand* grouped, const Counters* ct, const SortScratch* ss, con
     }
 }
 
+/* deterministic_order = 0: the candidates of every octave, in the order their atomics arrived (what the reference returns) */
+__global__ void __launch_bounds__( SORT_NT )
+k_compact_unsorted( const Cand* cand, int cand_stride, const Counters* ct, Cand* sorted )
+{
+    pdl_enter();
+    const int o = blockIdx.y, n = ct->ext_ct[o];
+    const Cand* src = cand + (size_t)o * cand_stride;
+    Cand* dst = sorted + ct->ext_ps[o];
+    for( int i = blockIdx.x * SORT_NT + threadIdx.x; i < n; i += gridDim.x * SORT_NT ) dst[i] = src[i];
+}
+
 cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted, Cand* sort_tmp,
                             int ext_capacity, Counters* ct, SortScratch* ss, cudaStream_t st, long long* launches )
 {
@@ -490,6 +501,11 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     SortShifts sh;
     for( int o = 0; o < MAX_OCT; o++ ) { int q = 0; while( o < L.n_oct && ( ( L.h[o] - 1 ) >> q ) >= SORT_NBY ) q++; sh.y[o] = q; }
     const int gx = std::max( 1, std::min( 4 * sm_count(), ( ext_capacity + SORT_NT - 1 ) / SORT_NT ) ) / std::max( 1, L.oct_end - L.oct_begin ) + 1;
+    if( !K.deterministic ) {
+        launch_pdl( k_compact_unsorted, dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, sorted );
+        if( launches ) *launches += 3;
+        return cudaGetLastError();
+    }
     launch_pdl( k_sort_count,   dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, ss, sh );
     launch_pdl( k_sort_scan,    dim3( L.n_oct ),     dim3( 1024 ),    0, st, ct, ss );
     launch_pdl( k_sort_scatter, dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, ss, sh, sort_tmp );

@@ -112,6 +112,7 @@ void build_consts( const psift_config& cfg, Consts& c, DescTables& t )
     c.norm_mode        = cfg.norm_mode;
     c.up_fac           = (int)cfg.upscale_factor;                          /* sift_pyramid.cu:283,297 float -> int */
     c.grid_size        = cfg.filter_grid_size;
+    c.deterministic    = cfg.deterministic_order != 0;
 
     const float dn_step = 1.0f / 8.0f;                                     /* sift_constants.cu:33-41 */
     const float dn_base = 0.5f * dn_step - 20.0f * dn_step;

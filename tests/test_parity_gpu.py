@@ -145,6 +145,23 @@ def test_wait_take_results_outlive_job_and_context():
         L.psift_result_block_free(blk)
 
 
+def test_arrival_order_and_refusals():
+    """psift_config.deterministic_order = 0 skips the sort (the reference's arrival order): the same keypoint SET;
+    a row band under ScaleDirect (every octave filtered from the whole input image) is refused, not computed wrongly."""
+    img = load("g640")
+    with capi.Context(capi.default_config()) as ctx:
+        want = ctx.extract(img)
+    cfg = capi.default_config(); cfg.deterministic_order = 0
+    with capi.Context(cfg) as ctx:
+        got = ctx.extract(img)
+    rep = parity.compare(got, want, skip_last_desc=False)
+    assert rep["ok_int"] and rep["xy_bitexact"] and rep["ori_bitexact"][0] == rep["ori_bitexact"][1] and rep["max_desc_l2"] == 0.0, rep
+    with capi.Context(capi.default_config(scaling="direct", downsampling=0)) as ctx:
+        with pytest.raises(capi.PsiftError, match="ScaleDirect"):
+            ctx.submit_band(img, 0, 256, 0)
+        assert ctx.extract(img).n_feat > 0                   # the context is still usable
+
+
 def test_reconfigure_and_resize():
     with capi.Context(capi.default_config()) as ctx:
         a = ctx.extract(load("g256"))
