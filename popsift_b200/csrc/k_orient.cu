@@ -239,15 +239,19 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
 /* Exclusive prefix sum of num_ori over all keypoints, per-octave descriptor counts, and the
  * descriptor -> keypoint map (s_orientation.cu:303-345; common/excl_blk_prefix_sum.h).  One block. */
 constexpr int PS_NT = 1024;
+constexpr int DESC_CLASSES = 64;
+__device__ __forceinline__ int desc_class( float sigma ) { return min( DESC_CLASSES - 1, max( 0, (int)( fabsf( sigma ) * 10.0f ) ) ); }
 __global__ void __launch_bounds__( PS_NT )
 k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* __restrict__ desc_map, int desc_capacity )
 {
     __shared__ int warp_sum[32];
     __shared__ int carry;
+    __shared__ int cls_ct[DESC_CLASSES], cls_at[DESC_CLASSES];
     pdl_enter();
     const int total = ct->ext_total;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if( threadIdx.x == 0 ) carry = 0;
+    if( threadIdx.x < DESC_CLASSES ) cls_ct[threadIdx.x] = 0;
     __syncthreads();
     for( int base = 0; base < total; base += PS_NT ) {
         const int i = base + threadIdx.x;
@@ -280,25 +284,45 @@ k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* 
             }
             ext[i].idx_ori = min( excl, desc_capacity );
             for( int k = 0; k < nv; k++ ) desc_map[excl + k] = i;
+            if( nv > 0 ) atomicAdd( &cls_ct[desc_class( ext[i].sigma )], nv );
         }
         __syncthreads();
         if( threadIdx.x == 0 ) carry += warp_sum[31];
         __syncthreads();
     }
+    /* work order of the descriptor kernel: largest footprints first (classes of sigma, descending; the order inside a
+     * class is whatever the atomics give - it decides only WHEN a descriptor is computed, never where it is stored) */
     if( threadIdx.x == 0 ) {
-        const int ori_total = min( carry, desc_capacity );
+        int at = 0;
+        for( int c = DESC_CLASSES - 1; c >= 0; c-- ) { cls_at[c] = at; at += cls_ct[c]; }
+    }
+    __syncthreads();
+    int* order = desc_map + desc_capacity;
+    for( int i = threadIdx.x; i < total; i += PS_NT ) {
+        const int nv = ext[i].num_ori;
+        if( nv > 0 ) {
+            const int first = ext[i].idx_ori;
+            const int at = atomicAdd( &cls_at[desc_class( ext[i].sigma )], nv );
+            for( int k = 0; k < nv; k++ ) order[at + k] = first + k;
+        }
+    }
+    /* one thread per octave (the two look-ups of an octave are dependent global loads: nine octaves in a row on one
+     * thread were most of this kernel's time) */
+    const int ori_total = min( carry, desc_capacity );
+    if( threadIdx.x < MAX_OCT ) {
+        const int o = threadIdx.x;
+        const int fe = ct->ext_ps[o], n = ct->ext_ct[o];
+        int lo = ori_total, hi = ori_total;
+        if( n > 0 ) {
+            lo = ext[fe].idx_ori;
+            hi = ( fe + n < total ) ? ext[fe + n].idx_ori : ori_total;
+        }
+        ct->ori_ps[o] = lo;
+        ct->ori_ct[o] = n > 0 ? hi - lo : 0;
+    }
+    if( threadIdx.x == 0 ) {
         ct->ori_total = ori_total;
         ct->need_desc = carry;
-        for( int o = 0; o < MAX_OCT; o++ ) {
-            const int fe = ct->ext_ps[o], n = ct->ext_ct[o];
-            int lo = ori_total, hi = ori_total;
-            if( n > 0 ) {
-                lo = ext[fe].idx_ori;
-                hi = ( fe + n < total ) ? ext[fe + n].idx_ori : ori_total;
-            }
-            ct->ori_ps[o] = lo;
-            ct->ori_ct[o] = n > 0 ? hi - lo : 0;
-        }
         ct->ori_ps[MAX_OCT] = ori_total;
     }
 }

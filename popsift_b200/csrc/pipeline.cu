@@ -365,7 +365,7 @@ static int alloc_keypoint_buffers( Slot& s, int ext_cap, int desc_cap )
     CU( cudaMalloc( &s.sort_tmp, sizeof(Cand) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.ext,    sizeof(psift_extremum) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.feat,   sizeof(psift_feature) * (size_t)ext_cap ) );
-    CU( cudaMalloc( &s.desc_map, sizeof(int) * (size_t)desc_cap ) );
+    CU( cudaMalloc( &s.desc_map, sizeof(int) * 2 * (size_t)desc_cap ) );   /* descriptor -> keypoint, then the work order */
     CU( cudaMalloc( &s.desc,   sizeof(float) * 128 * (size_t)desc_cap ) );
     CU( cudaMalloc( &s.filt, filter_scratch_bytes( ext_cap ) ) );
     return PSIFT_OK;
@@ -528,7 +528,7 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing, int parts = FRA
     CU( stamp( s.ev[3] ) );
     CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, c->n_sm * 10, st, &c->launches ) );
     CU( stamp( s.ev[4] ) );
-    CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.lintex_d, c->d_dt, s.desc, s.feat, c->n_sm * 4, st, &c->launches ) );
+    CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.desc_cap, s.lintex_d, c->d_dt, s.desc, s.feat, c->n_sm * 4, st, &c->launches ) );
     CU( stamp( s.ev[5] ) );
     CU( cudaMemcpyAsync( s.h_ct, s.ct, sizeof(Counters), cudaMemcpyDeviceToHost, st ) );
     if( !capturing ) return queue_result_copies( s );        /* a graph leaves them to run_frame: their target may change */
