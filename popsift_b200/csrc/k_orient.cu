@@ -242,7 +242,7 @@ constexpr int PS_NT = 1024;
 constexpr int DESC_CLASSES = 64;
 __device__ __forceinline__ int desc_class( float sigma ) { return min( DESC_CLASSES - 1, max( 0, (int)( fabsf( sigma ) * 10.0f ) ) ); }
 __global__ void __launch_bounds__( PS_NT )
-k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* __restrict__ desc_map, int desc_capacity )
+k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* __restrict__ desc_map, DescWork* __restrict__ work, int desc_capacity )
 {
     __shared__ int warp_sum[32];
     __shared__ int carry;
@@ -297,13 +297,13 @@ k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* 
         for( int c = DESC_CLASSES - 1; c >= 0; c-- ) { cls_at[c] = at; at += cls_ct[c]; }
     }
     __syncthreads();
-    int* order = desc_map + desc_capacity;
     for( int i = threadIdx.x; i < total; i += PS_NT ) {
-        const int nv = ext[i].num_ori;
-        if( nv > 0 ) {
-            const int first = ext[i].idx_ori;
-            const int at = atomicAdd( &cls_at[desc_class( ext[i].sigma )], nv );
-            for( int k = 0; k < nv; k++ ) order[at + k] = first + k;
+        const psift_extremum e = ext[i];
+        if( e.num_ori > 0 ) {
+            const int at = atomicAdd( &cls_at[desc_class( e.sigma )], e.num_ori );
+            DescWork w;
+            w.x = e.xpos; w.y = e.ypos; w.sigma = e.sigma; w.octave = e.octave; w.level = e.lpos; w.pad = 0;
+            for( int k = 0; k < e.num_ori; k++ ) { w.ang = e.orientation[k]; w.d = e.idx_ori + k; work[at + k] = w; }
         }
     }
     /* one thread per octave (the two look-ups of an octave are dependent global loads: nine octaves in a row on one
@@ -328,10 +328,10 @@ k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* 
 }
 
 cudaError_t launch_orientation( const PyrLayout& L, const Cand* sorted, Counters* ct, psift_extremum* ext,
-                                int* desc_map, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches )
+                                int* desc_map, DescWork* work, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches )
 {
     launch_pdl( k_orientation, dim3( n_blocks ), dim3( ORI_WARPS * 32 ), 0, st, L, sorted, ct, ext );
-    launch_pdl( k_ori_prefix, dim3( 1 ), dim3( PS_NT ), 0, st, ext, ct, desc_map, desc_capacity );
+    launch_pdl( k_ori_prefix, dim3( 1 ), dim3( PS_NT ), 0, st, ext, ct, desc_map, work, desc_capacity );
     if( launches ) *launches += 2;
     return cudaGetLastError();
 }

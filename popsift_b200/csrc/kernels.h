@@ -40,10 +40,10 @@ cudaError_t launch_match( const float* l, int l_len, const float* r, int r_len, 
 cudaError_t launch_ref_features( const psift_feature* in, int n, float* desc_base, void* out72, cudaStream_t st );
 /* k_orient.cu */
 cudaError_t launch_orientation( const PyrLayout& L, const Cand* sorted, Counters* ct, psift_extremum* ext,
-                                int* desc_map, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches );
+                                int* desc_map, DescWork* work, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches );
 /* k_desc.cu */
 cudaError_t launch_descriptors( const PyrLayout& L, const Consts& K, const psift_extremum* ext, Counters* ct,
-                                const int* desc_map, int desc_capacity, const cudaTextureObject_t* lintex, const DescTables* tab,
+                                const DescWork* work, const cudaTextureObject_t* lintex, const DescTables* tab,
                                 float* desc, psift_feature* feat, int n_blocks, cudaStream_t st, long long* launches );
 /* pipeline.cu: sets the calling thread's psift_last_error() text and returns `code` (for entry points that live in other files) */
 int set_error( int code, const char* msg );

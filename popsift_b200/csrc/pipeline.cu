@@ -81,6 +81,7 @@ struct Slot {
     psift_extremum* ext = nullptr;
     psift_feature*  feat = nullptr;
     int*   desc_map = nullptr;
+    DescWork* desc_work = nullptr;
     float* desc = nullptr;
     Counters* ct = nullptr;
     void*  filt = nullptr;                                  /* grid filter scratch */
@@ -142,7 +143,7 @@ static void free_slot( Slot& s )
     if( s.img_tex ) cudaDestroyTextureObject( s.img_tex );
     if( s.d_img ) cudaFree( s.d_img );
     if( s.h_img ) cudaFreeHost( s.h_img );
-    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
+    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc_work ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
     if( s.h_ct ) cudaFreeHost( s.h_ct );
     if( s.h_ext ) cudaFreeHost( s.h_ext );
     if( s.h_feat ) cudaFreeHost( s.h_feat );
@@ -358,14 +359,15 @@ static int bind_input_texture( Slot& s, const void* dptr, size_t pitch, int w, i
  * (Pyramid::reallocExtrema, sift_pyramid.cu:179-215); psift_wait() does the same and re-runs the frame. */
 static int alloc_keypoint_buffers( Slot& s, int ext_cap, int desc_cap )
 {
-    cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc ); cudaFree( s.filt );
-    s.sort_tmp = nullptr; s.sorted = nullptr; s.ext = nullptr; s.feat = nullptr; s.desc_map = nullptr; s.desc = nullptr; s.filt = nullptr;
+    cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc_work ); cudaFree( s.desc ); cudaFree( s.filt );
+    s.sort_tmp = nullptr; s.sorted = nullptr; s.ext = nullptr; s.feat = nullptr; s.desc_map = nullptr; s.desc_work = nullptr; s.desc = nullptr; s.filt = nullptr;
     s.ext_cap = ext_cap; s.desc_cap = desc_cap; s.epoch++;
     CU( cudaMalloc( &s.sorted, sizeof(Cand) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.sort_tmp, sizeof(Cand) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.ext,    sizeof(psift_extremum) * (size_t)ext_cap ) );
     CU( cudaMalloc( &s.feat,   sizeof(psift_feature) * (size_t)ext_cap ) );
-    CU( cudaMalloc( &s.desc_map, sizeof(int) * 2 * (size_t)desc_cap ) );   /* descriptor -> keypoint, then the work order */
+    CU( cudaMalloc( &s.desc_map, sizeof(int) * (size_t)desc_cap ) );
+    CU( cudaMalloc( &s.desc_work, sizeof(DescWork) * (size_t)desc_cap ) );
     CU( cudaMalloc( &s.desc,   sizeof(float) * 128 * (size_t)desc_cap ) );
     CU( cudaMalloc( &s.filt, filter_scratch_bytes( ext_cap ) ) );
     return PSIFT_OK;
@@ -526,9 +528,9 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing, int parts = FRA
     CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.sort_tmp, s.ext_cap, s.ct, &reinterpret_cast<CountersAndSort*>( s.ct )->ss, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
     CU( stamp( s.ev[3] ) );
-    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_cap, c->n_sm * 10, st, &c->launches ) );
+    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_work, s.desc_cap, c->n_sm * 10, st, &c->launches ) );
     CU( stamp( s.ev[4] ) );
-    CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_map, s.desc_cap, s.lintex_d, c->d_dt, s.desc, s.feat, c->n_sm * 4, st, &c->launches ) );
+    CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_work, s.lintex_d, c->d_dt, s.desc, s.feat, c->n_sm * 4, st, &c->launches ) );
     CU( stamp( s.ev[5] ) );
     CU( cudaMemcpyAsync( s.h_ct, s.ct, sizeof(Counters), cudaMemcpyDeviceToHost, st ) );
     if( !capturing ) return queue_result_copies( s );        /* a graph leaves them to run_frame: their target may change */
