@@ -183,6 +183,22 @@ __device__ bool refine_extremum( const DogView& dv, const Consts& k, int x, int 
     return true;
 }
 
+/* refinement of one strict extremum and, if it survives, its append to the octave's list (s_extrema.cu:22-44) */
+template<int MODE>
+__device__ __forceinline__ void refine_and_append( const DogView& dv, const Consts& K, int o, int x, int y, int level, float val,
+                                                   Cand* cand, int cand_stride, Counters* ct )
+{
+    const float w_div = __fdiv_rn( (float)dv.w, (float)K.grid_size );
+    const float h_div = __fdiv_rn( (float)dv.h, (float)K.grid_size );
+    Cand c;
+    if( refine_extremum<MODE>( dv, K, x, y, level, val, w_div, h_div, c ) ) {
+        c.key_lo = (uint32_t)x | ( (uint32_t)( y & 0xf ) << 28 );
+        c.key_hi = ( (uint32_t)y >> 4 ) | ( (uint32_t)level << 24 );
+        const int idx = atomicAdd( &ct->ext_ct[o], 1 );
+        if( idx < K.max_extrema ) cand[(size_t)o * cand_stride + idx] = c;
+    }
+}
+
 /* block -> (octave, tile) table */
 struct ExtGrid {
     int first_block[MAX_OCT + 1];
@@ -195,153 +211,218 @@ constexpr int EX_SH = EX_TY + 2;
 
 static size_t extrema_smem( int n_lvl )
 {
-    return sizeof(float) * (size_t)( n_lvl - 1 ) * EX_SH * EX_SW                  /* DoG tile            */
-         + sizeof(unsigned short) * 2 * (size_t)( n_lvl - 3 ) * EX_TX * EX_TY;    /* two survivor queues */
+    /* Strict extrema of one kind cannot be neighbours, so a tile of 64 x 16 x nl voxels holds at most
+     * 32 * 8 * ceil(nl / 2) maxima and as many minima: 256 * (nl + 1) entries bound the second queue. */
+    return sizeof(float) * 2 * (size_t)n_lvl * EX_SH * EX_SW                      /* two raw tiles (the DoG replaces one in place) */
+         + sizeof(float) * 256 * (size_t)( n_lvl - 2 )                            /* second queue: DoG values */
+         + sizeof(unsigned short) * (size_t)( n_lvl - 3 ) * EX_TX * EX_TY         /* first queue */
+         + sizeof(unsigned short) * 256 * (size_t)( n_lvl - 2 );                  /* second queue: voxels */
 }
 
-/* One block = one 64x16 tile of one octave, all levels.
- *   load    : every Gaussian level of the tile (+1 halo) is read once, coalesced; the DoG goes to smem
+/* Persistent blocks; one step = one 64x16 tile of one octave, all levels.
+ *   copy    : every Gaussian level of the NEXT tile (+1 halo) is requested with 16-byte asynchronous copies into the
+ *             second buffer before the current tile is looked at, so a block always has a tile's worth of reads in
+ *             flight and never waits for one (the one-tile-per-block version spent a memory latency per tile with
+ *             nothing else to do: 0.50 of the HBM bandwidth, profiles/r02h_ncu_frame_summary.txt)
+ *   DoG     : differences of neighbouring levels, in place
  *   phase 1 : first contrast test on each voxel's own value; survivors are queued (warp-aggregated)
  *   phase 2 : 26-neighbour test out of shared memory, balanced over the block; strict extrema queued
  *   phase 3 : Newton refinement for the few that are left (neighbours re-derived from the
  *             L2-resident Gaussian planes, since the iteration may walk out of the tile)
- * NLVL > 0 fixes the number of Gaussian levels at compile time (all loads of a pixel in flight
- * together); NLVL == 0 takes it from the layout. */
+ * NLVL > 0 fixes the number of Gaussian levels at compile time; NLVL == 0 takes it from the layout. */
 template<int MODE, int NLVL>
 __global__ void __launch_bounds__( EX_NT )
 k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid G, const __grid_constant__ Consts K,
-           Cand* cand, int cand_stride, Counters* ct )
+           Cand* cand, int cand_stride, Counters* ct, Surv* surv, int surv_cap )
 {
     extern __shared__ __align__( 16 ) float ex_smem[];
-    __shared__ int n1, n2;
+    __shared__ int n1[2], n2[2];
     pdl_enter();
     const int n_lvl = NLVL ? NLVL : L.n_lvl;
     const int qcap  = ( n_lvl - 3 ) * EX_TX * EX_TY;
-    float*          D  = ex_smem;                                             /* [n_lvl-1][EX_SH][EX_SW] */
-    unsigned short* q1 = reinterpret_cast<unsigned short*>( D + ( n_lvl - 1 ) * EX_SH * EX_SW );
-    unsigned short* q2 = q1 + qcap;
-
-    int o = 0;
-    while( o + 1 < L.n_oct && (int)blockIdx.x >= G.first_block[o + 1] ) o++;
-    const int tile = blockIdx.x - G.first_block[o];
-    const int w = L.w[o], h = L.h[o];
-    const int tx0 = ( tile % G.tiles_x[o] ) * EX_TX;
-    const int ty0 = L.row_lo[o] + ( tile / G.tiles_x[o] ) * EX_TY;
+    const int tile_floats = n_lvl * EX_SH * EX_SW;
+    float*          q2v = ex_smem + 2 * tile_floats;
+    unsigned short* q1  = reinterpret_cast<unsigned short*>( q2v + 256 * ( n_lvl - 2 ) );
+    unsigned short* q2  = q1 + qcap;
     const int tid = threadIdx.x;
-    if( tid == 0 ) { n1 = 0; n2 = 0; }
-
-    DogView dv;
-    dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = n_lvl;
-    dv.y_lo = L.row_lo[o]; dv.y_hi = L.row_hi[o];
-
-    /* ---- load: Gaussian levels -> DoG tile, four columns at a time ----
-     * Tile column x is stored at x+4: shared column 3 is the left halo, EX_TX+4 the right one.
-     * Columns outside the image are never looked at (candidates keep one pixel away from the
-     * border), so a float4 that would leave the row's allocation is simply not loaded. */
+    const int n_tiles = G.first_block[MAX_OCT];
     constexpr int LQ = EX_SW / 4;
-    for( int i = tid; i < EX_SH * LQ; i += EX_NT ) {
-        const int sy = i / LQ, c4 = i % LQ;
-        const int gx0 = tx0 - 4 + 4 * c4;
-        const int gy  = min( max( ty0 - 1 + sy, dv.y_lo ), dv.y_hi - 1 );
-        float4* d = reinterpret_cast<float4*>( D + sy * EX_SW ) + c4;
-        const bool ok = ( gx0 >= 0 ) && ( gx0 + 3 < dv.pitch );
-        const float4* p = reinterpret_cast<const float4*>( dv.base + (size_t)gy * dv.pitch + ( ok ? gx0 : 0 ) );
-        const size_t ls4 = dv.lstride / 4;                                  /* planes are 512-byte aligned */
-        if( NLVL ) {
-            float4 g[NLVL ? NLVL : 1];
-            #pragma unroll
-            for( int l = 0; l < NLVL; l++ ) g[l] = __ldg( p + l * ls4 );
-            #pragma unroll
-            for( int l = 0; l + 1 < NLVL; l++ )
-                d[l * ( EX_SH * EX_SW / 4 )] = make_float4( __fsub_rn( g[l + 1].x, g[l].x ), __fsub_rn( g[l + 1].y, g[l].y ),
-                                                            __fsub_rn( g[l + 1].z, g[l].z ), __fsub_rn( g[l + 1].w, g[l].w ) );
-        } else {
-            float4 prev = __ldg( p );
-            for( int l = 1; l < n_lvl; l++ ) {
-                const float4 cur = __ldg( p + l * ls4 );
-                d[( l - 1 ) * ( EX_SH * EX_SW / 4 )] = make_float4( __fsub_rn( cur.x, prev.x ), __fsub_rn( cur.y, prev.y ),
-                                                                    __fsub_rn( cur.z, prev.z ), __fsub_rn( cur.w, prev.w ) );
-                prev = cur;
+
+    /* Tile column x is stored at x+4: shared column 3 is the left halo, EX_TX+4 the right one.  Columns outside the
+     * image are never looked at (candidates keep one pixel away from the border), so a 16-byte chunk that would leave
+     * the row's allocation is not read (zeros instead); rows are clamped to the stored ones. */
+    auto request = [&]( int t, float* buf ) {
+        int o = 0;
+        while( o + 1 < L.n_oct && t >= G.first_block[o + 1] ) o++;
+        const int tile = t - G.first_block[o];
+        const int tx0 = ( tile % G.tiles_x[o] ) * EX_TX;
+        const int ty0 = L.row_lo[o] + ( tile / G.tiles_x[o] ) * EX_TY;
+        const int pitch = L.pitch[o], y_lo = L.row_lo[o], y_hi = L.row_hi[o];
+        const float* base = L.base[o];
+        const size_t lstride = L.lstride[o];
+        for( int i = tid; i < EX_SH * LQ; i += EX_NT ) {
+            const int sy = i / LQ, c4 = i % LQ;
+            const int gx0 = tx0 - 4 + 4 * c4;
+            const int gy  = min( max( ty0 - 1 + sy, y_lo ), y_hi - 1 );
+            float* d = buf + sy * EX_SW + 4 * c4;
+            if( ( gx0 >= 0 ) && ( gx0 + 3 < pitch ) ) {
+                const float* p = base + (size_t)gy * pitch + gx0;
+                unsigned da = (unsigned)__cvta_generic_to_shared( d );
+                for( int l = 0; l < n_lvl; l++, p += lstride, da += 4u * EX_SH * EX_SW )
+                    asm volatile( "cp.async.cg.shared.global [%0], [%1], 16;" :: "r"( da ), "l"( p ) : "memory" );
+            } else {
+                for( int l = 0; l < n_lvl; l++ ) *reinterpret_cast<float4*>( d + l * EX_SH * EX_SW ) = make_float4( 0.f, 0.f, 0.f, 0.f );
             }
         }
-    }
-    __syncthreads();
+        asm volatile( "cp.async.commit_group;" ::: "memory" );
+    };
 
-    /* ---- phase 1: first contrast test, four voxels per thread and level ---- */
-    {
-        const int g = tid % ( EX_TX / 4 ), y = tid / ( EX_TX / 4 );       /* 16 x 16 threads = 64 x 16 pixels */
-        const int gy = ty0 + y;
-        unsigned inside = 0;
-        #pragma unroll
-        for( int j = 0; j < 4; j++ ) {
-            const int gx = tx0 + 4 * g + j;
-            bool in = ( gx >= 1 ) && ( gy >= 1 ) && ( gx <= w - 2 ) && ( gy <= h - 2 );
-            in = in && ( gy >= L.own_lo[o] ) && ( gy < L.own_hi[o] );       /* banded: each voxel belongs to one context */
-            if( MODE == PSIFT_MODE_OPENCV ) in = in && !( gx < 5 || gy < 5 || gx >= w - 5 || gy >= h - 5 );   /* :336-340 */
-            inside |= in ? ( 1u << j ) : 0u;
-        }
-        if( inside )
-            for( int level = 1; level <= n_lvl - 3; level++ ) {
-                const float4 v = *reinterpret_cast<const float4*>( D + ( level * EX_SH + y + 1 ) * EX_SW + 4 * g + 4 );
-                unsigned m = ( first_contrast_ok<MODE>( v.x, K.threshold ) ? 1u : 0u ) | ( first_contrast_ok<MODE>( v.y, K.threshold ) ? 2u : 0u )
-                           | ( first_contrast_ok<MODE>( v.z, K.threshold ) ? 4u : 0u ) | ( first_contrast_ok<MODE>( v.w, K.threshold ) ? 8u : 0u );
-                m &= inside;
-                if( m ) {
-                    int pos = atomicAdd( &n1, __popc( m ) );
-                    #pragma unroll
-                    for( int j = 0; j < 4; j++ )
-                        if( m & ( 1u << j ) ) q1[pos++] = (unsigned short)( ( 4 * g + j ) | ( y << 6 ) | ( level << 10 ) );
+    /* Three block barriers per tile: the copies have landed / the queue of phase 1 is complete / the queue of phase 2
+     * is complete.  The counters alternate like the buffers, so a step never resets what a slow warp of the previous
+     * step still reads. */
+    int t = blockIdx.x, k = 0;
+    if( t < n_tiles ) request( t, ex_smem );
+    for( ; t < n_tiles; t += gridDim.x, k ^= 1 ) {
+        float* D = ex_smem + k * tile_floats;                                  /* [n_lvl][EX_SH][EX_SW]; DoG in [0, n_lvl-1) */
+        if( t + (int)gridDim.x < n_tiles ) request( t + gridDim.x, ex_smem + ( k ^ 1 ) * tile_floats );
+        else asm volatile( "cp.async.commit_group;" ::: "memory" );
+        asm volatile( "cp.async.wait_group 1;" ::: "memory" );
+        if( tid == 0 ) { n1[k] = 0; n2[k] = 0; }
+        __syncthreads();
+
+        int o = 0;
+        while( o + 1 < L.n_oct && t >= G.first_block[o + 1] ) o++;
+        const int tile = t - G.first_block[o];
+        const int w = L.w[o], h = L.h[o];
+        const int tx0 = ( tile % G.tiles_x[o] ) * EX_TX;
+        const int ty0 = L.row_lo[o] + ( tile / G.tiles_x[o] ) * EX_TY;
+
+        /* ---- DoG in place, four columns at a time; phase 1 (first contrast test) on the thread's own interior chunk
+         * straight from the registers.  Item i < 256 is the interior chunk (row y+1, chunk g+1) of thread i, the
+         * remaining 68 items are the halo chunks. ---- */
+        {
+            const int g = tid % ( EX_TX / 4 ), y = tid / ( EX_TX / 4 );       /* 16 x 16 threads = 64 x 16 pixels */
+            const int gy = ty0 + y;
+            unsigned inside = 0;
+            #pragma unroll
+            for( int j = 0; j < 4; j++ ) {
+                const int gx = tx0 + 4 * g + j;
+                bool in = ( gx >= 1 ) && ( gy >= 1 ) && ( gx <= w - 2 ) && ( gy <= h - 2 );
+                in = in && ( gy >= L.own_lo[o] ) && ( gy < L.own_hi[o] );       /* banded: each voxel belongs to one context */
+                if( MODE == PSIFT_MODE_OPENCV ) in = in && !( gx < 5 || gy < 5 || gx >= w - 5 || gy >= h - 5 );   /* :336-340 */
+                inside |= in ? ( 1u << j ) : 0u;
+            }
+            float4* d = reinterpret_cast<float4*>( D ) + ( y + 1 ) * LQ + g + 1;
+            float4 prev = d[0];
+            #pragma unroll
+            for( int l = 1; l < n_lvl; l++ ) {
+                const float4 cur = d[l * ( EX_SH * LQ )];
+                const float4 v = make_float4( __fsub_rn( cur.x, prev.x ), __fsub_rn( cur.y, prev.y ), __fsub_rn( cur.z, prev.z ), __fsub_rn( cur.w, prev.w ) );
+                d[( l - 1 ) * ( EX_SH * LQ )] = v;
+                prev = cur;
+                const int level = l - 1;
+                if( inside && level >= 1 && level <= n_lvl - 3 ) {
+                    unsigned m = ( first_contrast_ok<MODE>( v.x, K.threshold ) ? 1u : 0u ) | ( first_contrast_ok<MODE>( v.y, K.threshold ) ? 2u : 0u )
+                               | ( first_contrast_ok<MODE>( v.z, K.threshold ) ? 4u : 0u ) | ( first_contrast_ok<MODE>( v.w, K.threshold ) ? 8u : 0u );
+                    m &= inside;
+                    if( m ) {
+                        int pos = atomicAdd( &n1[k], __popc( m ) );
+                        #pragma unroll
+                        for( int j = 0; j < 4; j++ )
+                            if( m & ( 1u << j ) ) q1[pos++] = (unsigned short)( ( 4 * g + j ) | ( y << 6 ) | ( level << 10 ) );
+                    }
                 }
             }
-    }
-    __syncthreads();
-
-    /* ---- phase 2: strict maximum or minimum of the 26 neighbours (s_extrema.cu:56-120) ---- */
-    const int cnt1 = n1;
-    for( int i = tid; i < cnt1; i += EX_NT ) {
-        const unsigned e = q1[i];
-        const int x = e & 63, y = ( e >> 6 ) & 15, level = e >> 10;
-        const float* c = D + ( level * EX_SH + y + 1 ) * EX_SW + x + 4;
-        const float v = *c;
-        bool gt = true, lt = true;
-        #pragma unroll
-        for( int dy = -1; dy <= 1; dy++ )
-            #pragma unroll
-            for( int dx = -1; dx <= 1; dx++ ) {
-                if( dy == 0 && dx == 0 ) continue;
-                const float f = c[dy * EX_SW + dx];
-                gt = gt && ( v > f ); lt = lt && ( v < f );
+            if( tid < EX_SH * LQ - EX_NT ) {
+                /* halo chunks: rows 0 and EX_SH-1 (LQ chunks each), then chunks 0 and LQ-1 of the rows between */
+                int sy, c4;
+                if( tid < 2 * LQ ) { sy = tid < LQ ? 0 : EX_SH - 1; c4 = tid % LQ; }
+                else               { sy = 1 + ( tid - 2 * LQ ) / 2; c4 = ( ( tid - 2 * LQ ) & 1 ) ? LQ - 1 : 0; }
+                float4* e = reinterpret_cast<float4*>( D ) + sy * LQ + c4;
+                float4 pv = e[0];
+                for( int l = 1; l < n_lvl; l++ ) {
+                    const float4 cur = e[l * ( EX_SH * LQ )];
+                    e[( l - 1 ) * ( EX_SH * LQ )] = make_float4( __fsub_rn( cur.x, pv.x ), __fsub_rn( cur.y, pv.y ), __fsub_rn( cur.z, pv.z ), __fsub_rn( cur.w, pv.w ) );
+                    pv = cur;
+                }
             }
-        if( !gt && !lt ) continue;
-        #pragma unroll
-        for( int dz = -1; dz <= 1; dz += 2 )
+        }
+        __syncthreads();
+
+        /* ---- phase 2: strict maximum or minimum of the 26 neighbours (s_extrema.cu:56-120) ---- */
+        const int cnt1 = n1[k];
+        for( int i = tid; i < cnt1; i += EX_NT ) {
+            const unsigned e = q1[i];
+            const int x = e & 63, y = ( e >> 6 ) & 15, level = e >> 10;
+            const float* c = D + ( level * EX_SH + y + 1 ) * EX_SW + x + 4;
+            const float v = *c;
+            bool gt = true, lt = true;
             #pragma unroll
             for( int dy = -1; dy <= 1; dy++ )
                 #pragma unroll
                 for( int dx = -1; dx <= 1; dx++ ) {
-                    const float f = c[dz * EX_SH * EX_SW + dy * EX_SW + dx];
+                    if( dy == 0 && dx == 0 ) continue;
+                    const float f = c[dy * EX_SW + dx];
                     gt = gt && ( v > f ); lt = lt && ( v < f );
                 }
-        if( gt || lt ) q2[atomicAdd( &n2, 1 )] = (unsigned short)e;
-    }
-    __syncthreads();
-
-    /* ---- phase 3: refinement ---- */
-    const int cnt2 = n2;
-    if( cnt2 == 0 ) return;
-    const float w_div = __fdiv_rn( (float)w, (float)K.grid_size );
-    const float h_div = __fdiv_rn( (float)h, (float)K.grid_size );
-    for( int i = tid; i < cnt2; i += EX_NT ) {
-        const unsigned e = q2[i];
-        const int x = tx0 + ( e & 63 ), y = ty0 + ( ( e >> 6 ) & 15 ), level = e >> 10;
-        const float val = D[( level * EX_SH + ( y - ty0 ) + 1 ) * EX_SW + ( x - tx0 ) + 4];
-        Cand c;
-        if( refine_extremum<MODE>( dv, K, x, y, level, val, w_div, h_div, c ) ) {
-            c.key_lo = (uint32_t)x | ( (uint32_t)( y & 0xf ) << 28 );
-            c.key_hi = ( (uint32_t)y >> 4 ) | ( (uint32_t)level << 24 );
-            const int idx = atomicAdd( &ct->ext_ct[o], 1 );                 /* append, s_extrema.cu:22-44 */
-            if( idx < K.max_extrema ) cand[(size_t)o * cand_stride + idx] = c;
+            if( !gt && !lt ) continue;
+            #pragma unroll
+            for( int dz = -1; dz <= 1; dz += 2 )
+                #pragma unroll
+                for( int dy = -1; dy <= 1; dy++ )
+                    #pragma unroll
+                    for( int dx = -1; dx <= 1; dx++ ) {
+                        const float f = c[dz * EX_SH * EX_SW + dy * EX_SW + dx];
+                        gt = gt && ( v > f ); lt = lt && ( v < f );
+                    }
+            if( gt || lt ) { const int at = atomicAdd( &n2[k], 1 ); q2[at] = (unsigned short)e; q2v[at] = v; }
         }
+        __syncthreads();
+
+        /* ---- phase 3: the survivors go to the refinement list (k_refine: a block that refined its own few would keep
+         * 250 threads and its next tile waiting for one or two dependent walks through L2).  One warp; the others
+         * move on.  A full list (never seen; it holds max_extrema entries per octave) is refined here. ---- */
+        const int cnt2 = n2[k];
+        if( cnt2 > 0 && tid < 32 ) {
+            int at = 0;
+            if( tid == 0 ) at = atomicAdd( &ct->surv_n, cnt2 );
+            at = __shfl_sync( 0xffffffffu, at, 0 );
+            const bool fits = at + cnt2 <= surv_cap;
+            DogView dv;
+            dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = n_lvl;
+            dv.y_lo = L.row_lo[o]; dv.y_hi = L.row_hi[o];
+            for( int i = tid; i < cnt2; i += 32 ) {
+                const unsigned e = q2[i];
+                const int x = tx0 + ( e & 63 ), y = ty0 + ( ( e >> 6 ) & 15 ), level = e >> 10;
+                const float val = q2v[i];                                   /* not from the tile: its buffer is being refilled */
+                if( fits ) {
+                    Surv sv; sv.xy = (uint32_t)x | ( (uint32_t)y << 16 ); sv.lo = (uint32_t)level | ( (uint32_t)o << 8 ); sv.val = val; sv.pad = 0;
+                    surv[at + i] = sv;
+                } else {
+                    refine_and_append<MODE>( dv, K, o, x, y, level, val, cand, cand_stride, ct );
+                }
+            }
+        }
+        /* no barrier here: the next step writes the other buffer and the other counters, and its own barriers come
+         * before anything of this step is overwritten */
+    }
+}
+
+/* Newton refinement of the queued extrema (s_extrema.cu:122-330), one thread each, and the append to the octave's list */
+template<int MODE>
+__global__ void __launch_bounds__( 128 )
+k_refine( const __grid_constant__ PyrLayout L, const __grid_constant__ Consts K, const Surv* __restrict__ surv, int surv_cap,
+          Cand* cand, int cand_stride, Counters* ct )
+{
+    pdl_enter();
+    const int n = min( ct->surv_n, surv_cap );
+    for( int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x ) {
+        const Surv sv = surv[i];
+        const int o = (int)( sv.lo >> 8 ), level = (int)( sv.lo & 0xffu ), x = (int)( sv.xy & 0xffffu ), y = (int)( sv.xy >> 16 );
+        DogView dv;
+        dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = L.w[o]; dv.h = L.h[o]; dv.nlvl = L.n_lvl;
+        dv.y_lo = L.row_lo[o]; dv.y_hi = L.row_hi[o];
+        refine_and_append<MODE>( dv, K, o, x, y, level, sv.val, cand, cand_stride, ct );
     }
 }
 
@@ -465,7 +546,7 @@ k_compact_unsorted( const Cand* cand, int cand_stride, const Counters* ct, Cand*
     for( int i = blockIdx.x * SORT_NT + threadIdx.x; i < n; i += gridDim.x * SORT_NT ) dst[i] = src[i];
 }
 
-cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Cand* sorted, Cand* sort_tmp,
+cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Surv* surv, int surv_cap, Cand* sorted, Cand* sort_tmp,
                             int ext_capacity, Counters* ct, SortScratch* ss, cudaStream_t st, long long* launches )
 {
     ExtGrid G;
@@ -483,17 +564,29 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     if( L.n_lvl > 60 ) return cudaErrorInvalidValue;                      /* queue entries hold 6 bits of level */
 #define PSIFT_EXT_LAUNCH( MODE )                                                                             \
     do {                                                                                                      \
-        if( L.n_lvl == 6 ) launch_pdl( k_extrema<MODE, 6>, dim3( nb ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct ); \
-        else {                                                                                                \
-            cudaError_t e = cudaFuncSetAttribute( k_extrema<MODE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem ); \
-            if( e != cudaSuccess ) return e;                                                                  \
-            launch_pdl( k_extrema<MODE, 0>, dim3( nb ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct );       \
-        }                                                                                                     \
+        if( L.n_lvl == 6 ) { PSIFT_EXT_LAUNCH2( ( k_extrema<MODE, 6> ) ); }                                   \
+        else               { PSIFT_EXT_LAUNCH2( ( k_extrema<MODE, 0> ) ); }                                   \
+    } while( 0 )
+#define PSIFT_EXT_LAUNCH2( KERNEL )                                                                           \
+    do {                                                                                                      \
+        cudaError_t e = cudaFuncSetAttribute( KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem ); \
+        if( e != cudaSuccess ) return e;                                                                      \
+        int per_sm = 0;                                                                                       \
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor( &per_sm, KERNEL, EX_NT, smem );                    \
+        if( e != cudaSuccess || per_sm < 1 ) return e != cudaSuccess ? e : cudaErrorInvalidConfiguration;     \
+        const int blocks = std::min( nb, per_sm * sm_count() );                                               \
+        launch_pdl( KERNEL, dim3( blocks ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct, surv, surv_cap ); \
     } while( 0 )
     switch( K.sift_mode ) {
     case PSIFT_MODE_OPENCV: PSIFT_EXT_LAUNCH( PSIFT_MODE_OPENCV ); break;
     case PSIFT_MODE_VLFEAT: PSIFT_EXT_LAUNCH( PSIFT_MODE_VLFEAT ); break;
     default:                PSIFT_EXT_LAUNCH( PSIFT_MODE_POPSIFT ); break;
+    }
+#undef PSIFT_EXT_LAUNCH2
+    switch( K.sift_mode ) {
+    case PSIFT_MODE_OPENCV: launch_pdl( k_refine<PSIFT_MODE_OPENCV>,  dim3( sm_count() ), dim3( 128 ), 0, st, L, K, (const Surv*)surv, surv_cap, cand, cand_stride, ct ); break;
+    case PSIFT_MODE_VLFEAT: launch_pdl( k_refine<PSIFT_MODE_VLFEAT>,  dim3( sm_count() ), dim3( 128 ), 0, st, L, K, (const Surv*)surv, surv_cap, cand, cand_stride, ct ); break;
+    default:                launch_pdl( k_refine<PSIFT_MODE_POPSIFT>, dim3( sm_count() ), dim3( 128 ), 0, st, L, K, (const Surv*)surv, surv_cap, cand, cand_stride, ct ); break;
     }
 #undef PSIFT_EXT_LAUNCH
     launch_pdl( k_extrema_finish, dim3( 1 ), dim3( 32 ), 0, st, ct, L.n_oct, K.max_extrema, ext_capacity );
@@ -503,14 +596,14 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     const int gx = std::max( 1, std::min( 4 * sm_count(), ( ext_capacity + SORT_NT - 1 ) / SORT_NT ) ) / std::max( 1, L.oct_end - L.oct_begin ) + 1;
     if( !K.deterministic ) {
         launch_pdl( k_compact_unsorted, dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, sorted );
-        if( launches ) *launches += 3;
+        if( launches ) *launches += 4;
         return cudaGetLastError();
     }
     launch_pdl( k_sort_count,   dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, ss, sh );
     launch_pdl( k_sort_scan,    dim3( L.n_oct ),     dim3( 1024 ),    0, st, ct, ss );
     launch_pdl( k_sort_scatter, dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, ss, sh, sort_tmp );
     launch_pdl( k_sort_rank,    dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, sort_tmp, ct, ss, sh, sorted );
-    if( launches ) *launches += 6;
+    if( launches ) *launches += 7;
     return cudaGetLastError();
 }
 

@@ -82,6 +82,7 @@ struct Slot {
     psift_feature*  feat = nullptr;
     int*   desc_map = nullptr;
     DescWork* desc_work = nullptr;
+    Surv*  surv = nullptr;
     float* desc = nullptr;
     Counters* ct = nullptr;
     void*  filt = nullptr;                                  /* grid filter scratch */
@@ -143,7 +144,7 @@ static void free_slot( Slot& s )
     if( s.img_tex ) cudaDestroyTextureObject( s.img_tex );
     if( s.d_img ) cudaFree( s.d_img );
     if( s.h_img ) cudaFreeHost( s.h_img );
-    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc_work ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
+    cudaFree( s.cand ); cudaFree( s.surv ); cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc_work ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
     if( s.h_ct ) cudaFreeHost( s.h_ct );
     if( s.h_ext ) cudaFreeHost( s.h_ext );
     if( s.h_feat ) cudaFreeHost( s.h_feat );
@@ -389,6 +390,7 @@ static int init_slot( psift_ctx* c, Slot& s )
     const int me = c->cfg.max_extrema;
     s.cand_stride = me;
     CU( cudaMalloc( &s.cand,   sizeof(Cand) * (size_t)me * MAX_OCT ) );
+    CU( cudaMalloc( &s.surv,   sizeof(Surv) * (size_t)me * MAX_OCT ) );
     int rc = alloc_keypoint_buffers( s, me, std::max( 2 * me, me + me / 4 ) );   /* sift_pyramid.cu:148-159 */
     if( rc ) return rc;
     CU( cudaMalloc( &s.ct, sizeof(CountersAndSort) ) );           /* the counters, and behind them the sort's bucket counters */
@@ -525,7 +527,7 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing, int parts = FRA
     CU( launch_pyramid( L, s.img_tex, shift, powf( 2.0f, c->cfg.upscale_factor ), c->cfg.gauss_mode, c->cfg.scaling_mode, c->gt, s.ps, &c->launches ) );
     if( !( parts & FRAME_REST ) ) return PSIFT_OK;
     CU( stamp( s.ev[2] ) );
-    CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.sorted, s.sort_tmp, s.ext_cap, s.ct, &reinterpret_cast<CountersAndSort*>( s.ct )->ss, st, &c->launches ) );
+    CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.surv, s.cand_stride * MAX_OCT, s.sorted, s.sort_tmp, s.ext_cap, s.ct, &reinterpret_cast<CountersAndSort*>( s.ct )->ss, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
     CU( stamp( s.ev[3] ) );
     CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_work, s.desc_cap, c->n_sm * 10, st, &c->launches ) );
