@@ -37,6 +37,24 @@ struct DogView {
     }
 };
 
+/* The same values out of a tile of DoG levels in shared memory where it covers them (k_extrema: tile column x at x+4,
+ * row y at y+1), else from the planes: a Newton step rarely leaves the tile it started in. */
+struct TileView {
+    const float* D;                      /* [nlvl-1][rows][cols] */
+    int          tx0, ty0, cols, rows;
+    DogView      g;
+    int          w, h, nlvl;
+    __device__ __forceinline__ float at( int x, int y, int z ) const
+    {
+        x = min( max( x, 0 ), g.w - 1 );
+        y = min( max( y, g.y_lo ), g.y_hi - 1 );
+        z = min( max( z, 0 ), g.nlvl - 2 );
+        const int sx = x - tx0 + 4, sy = y - ty0 + 1;
+        if( (unsigned)( sx - 3 ) < (unsigned)( cols - 6 ) && (unsigned)sy < (unsigned)rows ) return D[( z * rows + sy ) * cols + sx];
+        return g.at( x, y, z );
+    }
+};
+
 /* strict maximum or strict minimum of the 26 neighbours (s_extrema.cu:56-120) */
 __device__ __forceinline__ bool strict_extremum( const DogView& d, int x, int y, int z, float v )
 {
@@ -112,8 +130,8 @@ __device__ __forceinline__ int step_rule( const float3& d, int3& n, int w, int h
     return 0;
 }
 
-template<int MODE>
-__device__ bool refine_extremum( const DogView& dv, const Consts& k, int x, int y, int level, float val,
+template<int MODE, class View>
+__device__ bool refine_extremum( const View& dv, const Consts& k, int x, int y, int level, float val,
                                  float w_div, float h_div, Cand& out )
 {
     const int w = dv.w, h = dv.h, maxlevel = dv.nlvl - 1;
@@ -184,8 +202,8 @@ __device__ bool refine_extremum( const DogView& dv, const Consts& k, int x, int 
 }
 
 /* refinement of one strict extremum and, if it survives, its append to the octave's list (s_extrema.cu:22-44) */
-template<int MODE>
-__device__ __forceinline__ void refine_and_append( const DogView& dv, const Consts& K, int o, int x, int y, int level, float val,
+template<int MODE, class View>
+__device__ __forceinline__ void refine_and_append( const View& dv, const Consts& K, int o, int x, int y, int level, float val,
                                                    Cand* cand, int cand_stride, Counters* ct )
 {
     const float w_div = __fdiv_rn( (float)dv.w, (float)K.grid_size );
@@ -233,10 +251,11 @@ static size_t extrema_smem( int n_lvl )
 template<int MODE, int NLVL>
 __global__ void __launch_bounds__( EX_NT )
 k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid G, const __grid_constant__ Consts K,
-           Cand* cand, int cand_stride, Counters* ct, Surv* surv, int surv_cap )
+           const unsigned char* tmaps, Cand* cand, int cand_stride, Counters* ct )
 {
-    extern __shared__ __align__( 16 ) float ex_smem[];
+    extern __shared__ __align__( 128 ) float ex_smem[];
     __shared__ int n1[2], n2[2];
+    __shared__ __align__( 8 ) unsigned long long bars[2];
     pdl_enter();
     const int n_lvl = NLVL ? NLVL : L.n_lvl;
     const int qcap  = ( n_lvl - 3 ) * EX_TX * EX_TY;
@@ -248,47 +267,45 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     const int n_tiles = G.first_block[MAX_OCT];
     constexpr int LQ = EX_SW / 4;
 
-    /* Tile column x is stored at x+4: shared column 3 is the left halo, EX_TX+4 the right one.  Columns outside the
-     * image are never looked at (candidates keep one pixel away from the border), so a 16-byte chunk that would leave
-     * the row's allocation is not read (zeros instead); rows are clamped to the stored ones. */
-    auto request = [&]( int t, float* buf ) {
+    /* Tile column x is stored at x+4: shared column 3 is the left halo, EX_TX+4 the right one.  One thread asks the
+     * TMA unit for the whole box (72 columns x 18 rows x all levels = one request); completion is counted in bytes on
+     * the buffer's mbarrier. */
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared( bars );
+    const unsigned buf0 = (unsigned)__cvta_generic_to_shared( ex_smem );
+    const unsigned tile_bytes = 4u * tile_floats;
+    auto request = [&]( int t, int kb ) {
         int o = 0;
         while( o + 1 < L.n_oct && t >= G.first_block[o + 1] ) o++;
         const int tile = t - G.first_block[o];
         const int tx0 = ( tile % G.tiles_x[o] ) * EX_TX;
-        const int ty0 = L.row_lo[o] + ( tile / G.tiles_x[o] ) * EX_TY;
-        const int pitch = L.pitch[o], y_lo = L.row_lo[o], y_hi = L.row_hi[o];
-        const float* base = L.base[o];
-        const size_t lstride = L.lstride[o];
-        for( int i = tid; i < EX_SH * LQ; i += EX_NT ) {
-            const int sy = i / LQ, c4 = i % LQ;
-            const int gx0 = tx0 - 4 + 4 * c4;
-            const int gy  = min( max( ty0 - 1 + sy, y_lo ), y_hi - 1 );
-            float* d = buf + sy * EX_SW + 4 * c4;
-            if( ( gx0 >= 0 ) && ( gx0 + 3 < pitch ) ) {
-                const float* p = base + (size_t)gy * pitch + gx0;
-                unsigned da = (unsigned)__cvta_generic_to_shared( d );
-                for( int l = 0; l < n_lvl; l++, p += lstride, da += 4u * EX_SH * EX_SW )
-                    asm volatile( "cp.async.cg.shared.global [%0], [%1], 16;" :: "r"( da ), "l"( p ) : "memory" );
-            } else {
-                for( int l = 0; l < n_lvl; l++ ) *reinterpret_cast<float4*>( d + l * EX_SH * EX_SW ) = make_float4( 0.f, 0.f, 0.f, 0.f );
-            }
-        }
-        asm volatile( "cp.async.commit_group;" ::: "memory" );
+        const int ty  = ( tile / G.tiles_x[o] ) * EX_TY;                         /* relative to the first stored row */
+        asm volatile( "fence.proxy.async.shared::cta;" ::: "memory" );            /* the buffer was last written by ordinary stores (DoG) */
+        asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"( bar0 + 8u * kb ), "r"( tile_bytes ) : "memory" );
+        asm volatile( "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                      :: "r"( buf0 + kb * tile_bytes ), "l"( tmaps + 128 * o ), "r"( tx0 - 4 ), "r"( ty - 1 ), "r"( 0 ), "r"( bar0 + 8u * kb ) : "memory" );
     };
+    if( tid == 0 ) {
+        asm volatile( "mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"( bar0 ) : "memory" );
+        asm volatile( "mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"( bar0 + 8u ) : "memory" );
+        asm volatile( "fence.mbarrier_init.release.cluster;" ::: "memory" );
+        n1[0] = n2[0] = n1[1] = n2[1] = 0;
+    }
+    __syncthreads();
 
-    /* Three block barriers per tile: the copies have landed / the queue of phase 1 is complete / the queue of phase 2
-     * is complete.  The counters alternate like the buffers, so a step never resets what a slow warp of the previous
-     * step still reads. */
+    /* Per tile: wait for the box / DoG + phase 1 / barrier / phase 2 / barrier / hand the survivors on.  Buffers, mbarriers
+     * and counters alternate, so a step never resets or refills what a slow warp of the previous step still reads. */
     int t = blockIdx.x, k = 0;
-    if( t < n_tiles ) request( t, ex_smem );
+    unsigned parity = 0;                                                          /* bit k: phase of buffer k's mbarrier */
+    if( tid == 0 && t < n_tiles ) request( t, 0 );
     for( ; t < n_tiles; t += gridDim.x, k ^= 1 ) {
         float* D = ex_smem + k * tile_floats;                                  /* [n_lvl][EX_SH][EX_SW]; DoG in [0, n_lvl-1) */
-        if( t + (int)gridDim.x < n_tiles ) request( t + gridDim.x, ex_smem + ( k ^ 1 ) * tile_floats );
-        else asm volatile( "cp.async.commit_group;" ::: "memory" );
-        asm volatile( "cp.async.wait_group 1;" ::: "memory" );
-        if( tid == 0 ) { n1[k] = 0; n2[k] = 0; }
-        __syncthreads();
+        if( tid == 0 ) {
+            n1[k ^ 1] = 0; n2[k ^ 1] = 0;                                      /* the next step's counters */
+            if( t + (int)gridDim.x < n_tiles ) request( t + gridDim.x, k ^ 1 );
+        }
+        asm volatile( "{\n\t.reg .pred p;\n\tEXW:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra EXD;\n\tbra EXW;\n\tEXD:\n\t}"
+                      :: "r"( bar0 + 8u * k ), "r"( ( parity >> k ) & 1u ) : "memory" );
+        parity ^= 1u << k;
 
         int o = 0;
         while( o + 1 < L.n_oct && t >= G.first_block[o + 1] ) o++;
@@ -379,50 +396,25 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
         }
         __syncthreads();
 
-        /* ---- phase 3: the survivors go to the refinement list (k_refine: a block that refined its own few would keep
-         * 250 threads and its next tile waiting for one or two dependent walks through L2).  One warp; the others
-         * move on.  A full list (never seen; it holds max_extrema entries per octave) is refined here. ---- */
+        /* ---- phase 3: Newton refinement of the few that are left, by the first warp while the others move on to the
+         * next tile (they meet again at its first barrier).  The first step - for nine in ten the only one - finds its
+         * 19 DoG values in the tile; a step that walks out of it reads the planes.  Thread 0 asks for the next box only
+         * after this, so the tile is still in place. ---- */
         const int cnt2 = n2[k];
         if( cnt2 > 0 && tid < 32 ) {
-            int at = 0;
-            if( tid == 0 ) at = atomicAdd( &ct->surv_n, cnt2 );
-            at = __shfl_sync( 0xffffffffu, at, 0 );
-            const bool fits = at + cnt2 <= surv_cap;
-            DogView dv;
-            dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = n_lvl;
-            dv.y_lo = L.row_lo[o]; dv.y_hi = L.row_hi[o];
+            TileView tv;
+            tv.D = D; tv.tx0 = tx0; tv.ty0 = ty0; tv.cols = EX_SW; tv.rows = EX_SH;
+            tv.g.base = L.base[o]; tv.g.lstride = L.lstride[o]; tv.g.pitch = L.pitch[o]; tv.g.w = w; tv.g.h = h; tv.g.nlvl = n_lvl;
+            tv.g.y_lo = L.row_lo[o]; tv.g.y_hi = L.row_hi[o];
+            tv.w = w; tv.h = h; tv.nlvl = n_lvl;
             for( int i = tid; i < cnt2; i += 32 ) {
                 const unsigned e = q2[i];
                 const int x = tx0 + ( e & 63 ), y = ty0 + ( ( e >> 6 ) & 15 ), level = e >> 10;
-                const float val = q2v[i];                                   /* not from the tile: its buffer is being refilled */
-                if( fits ) {
-                    Surv sv; sv.xy = (uint32_t)x | ( (uint32_t)y << 16 ); sv.lo = (uint32_t)level | ( (uint32_t)o << 8 ); sv.val = val; sv.pad = 0;
-                    surv[at + i] = sv;
-                } else {
-                    refine_and_append<MODE>( dv, K, o, x, y, level, val, cand, cand_stride, ct );
-                }
+                refine_and_append<MODE>( tv, K, o, x, y, level, q2v[i], cand, cand_stride, ct );
             }
         }
-        /* no barrier here: the next step writes the other buffer and the other counters, and its own barriers come
+        /* no barrier here: the next step uses the other buffer and the other counters, and its own barriers come
          * before anything of this step is overwritten */
-    }
-}
-
-/* Newton refinement of the queued extrema (s_extrema.cu:122-330), one thread each, and the append to the octave's list */
-template<int MODE>
-__global__ void __launch_bounds__( 128 )
-k_refine( const __grid_constant__ PyrLayout L, const __grid_constant__ Consts K, const Surv* __restrict__ surv, int surv_cap,
-          Cand* cand, int cand_stride, Counters* ct )
-{
-    pdl_enter();
-    const int n = min( ct->surv_n, surv_cap );
-    for( int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x ) {
-        const Surv sv = surv[i];
-        const int o = (int)( sv.lo >> 8 ), level = (int)( sv.lo & 0xffu ), x = (int)( sv.xy & 0xffffu ), y = (int)( sv.xy >> 16 );
-        DogView dv;
-        dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = L.w[o]; dv.h = L.h[o]; dv.nlvl = L.n_lvl;
-        dv.y_lo = L.row_lo[o]; dv.y_hi = L.row_hi[o];
-        refine_and_append<MODE>( dv, K, o, x, y, level, sv.val, cand, cand_stride, ct );
     }
 }
 
@@ -546,7 +538,9 @@ k_compact_unsorted( const Cand* cand, int cand_stride, const Counters* ct, Cand*
     for( int i = blockIdx.x * SORT_NT + threadIdx.x; i < n; i += gridDim.x * SORT_NT ) dst[i] = src[i];
 }
 
-cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Surv* surv, int surv_cap, Cand* sorted, Cand* sort_tmp,
+void extrema_box( int* columns, int* rows ) { *columns = EX_SW; *rows = EX_SH; }
+
+cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, const void* tensor_maps, Cand* cand, int cand_stride, Cand* sorted, Cand* sort_tmp,
                             int ext_capacity, Counters* ct, SortScratch* ss, cudaStream_t st, long long* launches )
 {
     ExtGrid G;
@@ -575,7 +569,7 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor( &per_sm, KERNEL, EX_NT, smem );                    \
         if( e != cudaSuccess || per_sm < 1 ) return e != cudaSuccess ? e : cudaErrorInvalidConfiguration;     \
         const int blocks = std::min( nb, per_sm * sm_count() );                                               \
-        launch_pdl( KERNEL, dim3( blocks ), dim3( EX_NT ), smem, st, L, G, K, cand, cand_stride, ct, surv, surv_cap ); \
+        launch_pdl( KERNEL, dim3( blocks ), dim3( EX_NT ), smem, st, L, G, K, (const unsigned char*)tensor_maps, cand, cand_stride, ct );  \
     } while( 0 )
     switch( K.sift_mode ) {
     case PSIFT_MODE_OPENCV: PSIFT_EXT_LAUNCH( PSIFT_MODE_OPENCV ); break;
@@ -583,12 +577,6 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     default:                PSIFT_EXT_LAUNCH( PSIFT_MODE_POPSIFT ); break;
     }
 #undef PSIFT_EXT_LAUNCH2
-    switch( K.sift_mode ) {
-    case PSIFT_MODE_OPENCV: launch_pdl( k_refine<PSIFT_MODE_OPENCV>,  dim3( sm_count() ), dim3( 128 ), 0, st, L, K, (const Surv*)surv, surv_cap, cand, cand_stride, ct ); break;
-    case PSIFT_MODE_VLFEAT: launch_pdl( k_refine<PSIFT_MODE_VLFEAT>,  dim3( sm_count() ), dim3( 128 ), 0, st, L, K, (const Surv*)surv, surv_cap, cand, cand_stride, ct ); break;
-    default:                launch_pdl( k_refine<PSIFT_MODE_POPSIFT>, dim3( sm_count() ), dim3( 128 ), 0, st, L, K, (const Surv*)surv, surv_cap, cand, cand_stride, ct ); break;
-    }
-#undef PSIFT_EXT_LAUNCH
     launch_pdl( k_extrema_finish, dim3( 1 ), dim3( 32 ), 0, st, ct, L.n_oct, K.max_extrema, ext_capacity );
     /* order the candidates (ss was zeroed together with the counters at the start of the frame) */
     SortShifts sh;
@@ -596,14 +584,14 @@ cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int
     const int gx = std::max( 1, std::min( 4 * sm_count(), ( ext_capacity + SORT_NT - 1 ) / SORT_NT ) ) / std::max( 1, L.oct_end - L.oct_begin ) + 1;
     if( !K.deterministic ) {
         launch_pdl( k_compact_unsorted, dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, sorted );
-        if( launches ) *launches += 4;
+        if( launches ) *launches += 3;
         return cudaGetLastError();
     }
     launch_pdl( k_sort_count,   dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, ss, sh );
     launch_pdl( k_sort_scan,    dim3( L.n_oct ),     dim3( 1024 ),    0, st, ct, ss );
     launch_pdl( k_sort_scatter, dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, cand, cand_stride, ct, ss, sh, sort_tmp );
     launch_pdl( k_sort_rank,    dim3( gx, L.n_oct ), dim3( SORT_NT ), 0, st, sort_tmp, ct, ss, sh, sorted );
-    if( launches ) *launches += 7;
+    if( launches ) *launches += 6;
     return cudaGetLastError();
 }
 

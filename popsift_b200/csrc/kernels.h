@@ -29,7 +29,8 @@ cudaError_t launch_pyramid( const PyrLayout& L, cudaTextureObject_t input_tex, f
 cudaError_t launch_pyramid_level( const PyrLayout& L, int o, int l, cudaTextureObject_t input_tex, float shift, int gauss_mode,
                                   const GaussTables& T, cudaStream_t st );
 /* k_extrema.cu */
-cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, Cand* cand, int cand_stride, Surv* surv, int surv_cap, Cand* sorted, Cand* sort_tmp,
+void extrema_box( int* columns, int* rows );      /* box of the octaves' tensor maps: one tile plus halo */
+cudaError_t launch_extrema( const PyrLayout& L, const Consts& K, const void* tensor_maps, Cand* cand, int cand_stride, Cand* sorted, Cand* sort_tmp,
                             int ext_capacity, Counters* ct, SortScratch* ss, cudaStream_t st, long long* launches );
 /* k_filter.cu */
 size_t filter_scratch_bytes( int ext_capacity );

@@ -14,6 +14,7 @@
  */
 #include "common.h"
 #include "kernels.h"
+#include <cuda.h>                 /* CUtensorMap: the driver entry point is fetched through the runtime, nothing links libcuda */
 #include <cstdio>
 #include <cstring>
 #include <cstdarg>
@@ -72,6 +73,7 @@ struct Slot {
     int reg_kind = 0, reg_a = 0, reg_b = 0, reg_c = 0, reg_exchange = 0;   /* region the layout was built for (see Region) */
     std::vector<cudaTextureObject_t> lintex_h;
     cudaTextureObject_t* lintex_d = nullptr;
+    void*  tmaps_d = nullptr;            /* MAX_OCT tensor maps (TMA descriptors) of the octaves' level stacks, for k_extrema */
     std::vector<cudaTextureObject_t> scratch_tex;          /* Gauss mode "relative": the scratch plane, one view per octave */
     float* scratch = nullptr;
 
@@ -82,7 +84,6 @@ struct Slot {
     psift_feature*  feat = nullptr;
     int*   desc_map = nullptr;
     DescWork* desc_work = nullptr;
-    Surv*  surv = nullptr;
     float* desc = nullptr;
     Counters* ct = nullptr;
     void*  filt = nullptr;                                  /* grid filter scratch */
@@ -134,6 +135,7 @@ static void free_slot_pyramid( Slot& s )
     for( auto t : s.scratch_tex ) if( t ) cudaDestroyTextureObject( t );
     s.scratch_tex.clear();
     if( s.lintex_d ) { cudaFree( s.lintex_d ); s.lintex_d = nullptr; }
+    if( s.tmaps_d ) { cudaFree( s.tmaps_d ); s.tmaps_d = nullptr; }
     if( s.arena ) { cudaFree( s.arena ); s.arena = nullptr; s.arena_floats = 0; }
     s.in_w = s.in_h = 0;
 }
@@ -144,7 +146,7 @@ static void free_slot( Slot& s )
     if( s.img_tex ) cudaDestroyTextureObject( s.img_tex );
     if( s.d_img ) cudaFree( s.d_img );
     if( s.h_img ) cudaFreeHost( s.h_img );
-    cudaFree( s.cand ); cudaFree( s.surv ); cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc_work ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
+    cudaFree( s.cand ); cudaFree( s.sorted ); cudaFree( s.sort_tmp ); cudaFree( s.ext ); cudaFree( s.feat ); cudaFree( s.desc_map ); cudaFree( s.desc_work ); cudaFree( s.desc ); cudaFree( s.ct ); cudaFree( s.filt );
     if( s.h_ct ) cudaFreeHost( s.h_ct );
     if( s.h_ext ) cudaFreeHost( s.h_ext );
     if( s.h_feat ) cudaFreeHost( s.h_feat );
@@ -289,6 +291,37 @@ static int setup_pyramid_impl( psift_ctx* c, Slot& s, int w, int h, const Region
     s.L = L; s.in_w = w; s.in_h = h; s.epoch++;
     s.reg_kind = reg.kind; s.reg_a = reg.y0; s.reg_b = reg.y1; s.reg_c = reg.split; s.reg_exchange = reg.exchange;
 
+    /* TMA descriptors: every octave's stack of levels as a 3-D tensor (column, stored row, level), read by k_extrema in
+     * boxes of one tile plus halo.  Columns go up to the pitch (the padding is readable), rows are the stored ones:
+     * a box that sticks out is filled with zeros, which no candidate ever looks at. */
+    {
+        typedef CUresult ( *EncodeFn )( CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                        const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                        CUtensorMapL2promotion, CUtensorMapFloatOOBfill );
+        static EncodeFn encode = nullptr;
+        if( !encode ) {
+            void* fn = nullptr; cudaDriverEntryPointQueryResult qr;
+            CU( cudaGetDriverEntryPoint( "cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr ) );
+            if( !fn || qr != cudaDriverEntryPointSuccess ) return fail( PSIFT_E_CUDA, "cuTensorMapEncodeTiled is not available in this driver" );
+            encode = (EncodeFn)fn;
+        }
+        std::vector<CUtensorMap> maps( MAX_OCT );
+        memset( maps.data(), 0, sizeof(CUtensorMap) * MAX_OCT );
+        int box_w = 0, box_h = 0; extrema_box( &box_w, &box_h );
+        for( int o = L.oct_begin; o < L.oct_end; o++ ) {
+            const cuuint64_t dims[3]    = { (cuuint64_t)L.pitch[o], (cuuint64_t)( L.row_hi[o] - L.row_lo[o] ), (cuuint64_t)n_lvl };
+            const cuuint64_t strides[2] = { (cuuint64_t)L.pitch[o] * sizeof(float), (cuuint64_t)L.lstride[o] * sizeof(float) };
+            const cuuint32_t box[3]     = { (cuuint32_t)box_w, (cuuint32_t)box_h, (cuuint32_t)n_lvl };
+            const cuuint32_t estr[3]    = { 1, 1, 1 };
+            void* first = L.base[o] + (size_t)L.row_lo[o] * L.pitch[o];
+            const CUresult r = encode( &maps[o], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, first, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE );
+            if( r != CUDA_SUCCESS ) return fail( PSIFT_E_CUDA, "cuTensorMapEncodeTiled failed (%d) for octave %d", (int)r, o );
+        }
+        if( !s.tmaps_d ) CU( cudaMalloc( &s.tmaps_d, sizeof(CUtensorMap) * MAX_OCT ) );
+        CU( cudaMemcpy( s.tmaps_d, maps.data(), sizeof(CUtensorMap) * MAX_OCT, cudaMemcpyHostToDevice ) );
+    }
+
     if( linear_needed( c->cfg.desc_mode ) || relative ) {
         /* bilinear point-of-view of every Gaussian level (Octave::alloc_data_tex, sift_octave.cu:211-248) */
         s.lintex_h.assign( (size_t)n_oct * n_lvl, 0 );
@@ -390,7 +423,6 @@ static int init_slot( psift_ctx* c, Slot& s )
     const int me = c->cfg.max_extrema;
     s.cand_stride = me;
     CU( cudaMalloc( &s.cand,   sizeof(Cand) * (size_t)me * MAX_OCT ) );
-    CU( cudaMalloc( &s.surv,   sizeof(Surv) * (size_t)me * MAX_OCT ) );
     int rc = alloc_keypoint_buffers( s, me, std::max( 2 * me, me + me / 4 ) );   /* sift_pyramid.cu:148-159 */
     if( rc ) return rc;
     CU( cudaMalloc( &s.ct, sizeof(CountersAndSort) ) );           /* the counters, and behind them the sort's bucket counters */
@@ -527,7 +559,7 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing, int parts = FRA
     CU( launch_pyramid( L, s.img_tex, shift, powf( 2.0f, c->cfg.upscale_factor ), c->cfg.gauss_mode, c->cfg.scaling_mode, c->gt, s.ps, &c->launches ) );
     if( !( parts & FRAME_REST ) ) return PSIFT_OK;
     CU( stamp( s.ev[2] ) );
-    CU( launch_extrema( L, c->K, s.cand, s.cand_stride, s.surv, s.cand_stride * MAX_OCT, s.sorted, s.sort_tmp, s.ext_cap, s.ct, &reinterpret_cast<CountersAndSort*>( s.ct )->ss, st, &c->launches ) );
+    CU( launch_extrema( L, c->K, s.tmaps_d, s.cand, s.cand_stride, s.sorted, s.sort_tmp, s.ext_cap, s.ct, &reinterpret_cast<CountersAndSort*>( s.ct )->ss, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
     CU( stamp( s.ev[3] ) );
     CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_work, s.desc_cap, c->n_sm * 10, st, &c->launches ) );
