@@ -37,24 +37,6 @@ struct DogView {
     }
 };
 
-/* The same values out of a tile of DoG levels in shared memory where it covers them (k_extrema: tile column x at x+4,
- * row y at y+1), else from the planes: a Newton step rarely leaves the tile it started in. */
-struct TileView {
-    const float* D;                      /* [nlvl-1][rows][cols] */
-    int          tx0, ty0, cols, rows;
-    DogView      g;
-    int          w, h, nlvl;
-    __device__ __forceinline__ float at( int x, int y, int z ) const
-    {
-        x = min( max( x, 0 ), g.w - 1 );
-        y = min( max( y, g.y_lo ), g.y_hi - 1 );
-        z = min( max( z, 0 ), g.nlvl - 2 );
-        const int sx = x - tx0 + 4, sy = y - ty0 + 1;
-        if( (unsigned)( sx - 3 ) < (unsigned)( cols - 6 ) && (unsigned)sy < (unsigned)rows ) return D[( z * rows + sy ) * cols + sx];
-        return g.at( x, y, z );
-    }
-};
-
 /* strict maximum or strict minimum of the 26 neighbours (s_extrema.cu:56-120) */
 __device__ __forceinline__ bool strict_extremum( const DogView& d, int x, int y, int z, float v )
 {
@@ -217,6 +199,18 @@ __device__ __forceinline__ void refine_and_append( const View& dv, const Consts&
     }
 }
 
+/* one queued extremum: x | y << 16, level | octave << 8, DoG value */
+template<int MODE>
+__device__ __forceinline__ void refine_pending( const PyrLayout& L, const Consts& K, int n_lvl, unsigned xy, unsigned lo, float val,
+                                                Cand* cand, int cand_stride, Counters* ct )
+{
+    const int o = (int)( lo >> 8 );
+    DogView dv;
+    dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = L.w[o]; dv.h = L.h[o]; dv.nlvl = n_lvl;
+    dv.y_lo = L.row_lo[o]; dv.y_hi = L.row_hi[o];
+    refine_and_append<MODE>( dv, K, o, (int)( xy & 0xffffu ), (int)( xy >> 16 ), (int)( lo & 0xffu ), val, cand, cand_stride, ct );
+}
+
 /* block -> (octave, tile) table */
 struct ExtGrid {
     int first_block[MAX_OCT + 1];
@@ -226,6 +220,7 @@ struct ExtGrid {
 constexpr int EX_TX = 64, EX_TY = 16, EX_NT = 256;
 constexpr int EX_SW = EX_TX + 8;           /* DoG tile row: tile column x sits at x+4, so that rows load and read as float4 */
 constexpr int EX_SH = EX_TY + 2;
+constexpr int EX_PEND = 96;                 /* strict extrema of a block waiting for their refinement */
 
 static size_t extrema_smem( int n_lvl )
 {
@@ -256,6 +251,9 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
     extern __shared__ __align__( 128 ) float ex_smem[];
     __shared__ int n1[2], n2[2];
     __shared__ __align__( 8 ) unsigned long long bars[2];
+    __shared__ unsigned pend_xy[EX_PEND], pend_lo[EX_PEND];
+    __shared__ float    pend_val[EX_PEND];
+    int n_pend = 0;                                                             /* first warp only (uniform in it) */
     pdl_enter();
     const int n_lvl = NLVL ? NLVL : L.n_lvl;
     const int qcap  = ( n_lvl - 3 ) * EX_TX * EX_TY;
@@ -396,26 +394,39 @@ k_extrema( const __grid_constant__ PyrLayout L, const __grid_constant__ ExtGrid 
         }
         __syncthreads();
 
-        /* ---- phase 3: Newton refinement of the few that are left, by the first warp while the others move on to the
-         * next tile (they meet again at its first barrier).  The first step - for nine in ten the only one - finds its
-         * 19 DoG values in the tile; a step that walks out of it reads the planes.  Thread 0 asks for the next box only
-         * after this, so the tile is still in place. ---- */
+        /* ---- phase 3: the few that are left wait in a list of the block; whenever 32 have come together the first
+         * warp refines them, one per lane, while the others move on to the next tile (they meet again at its first
+         * barrier).  Two in five tiles leave one or two survivors: refining them at once kept the block waiting for a
+         * warp with one busy lane (1.3 us of dependent arithmetic) every other tile. ---- */
         const int cnt2 = n2[k];
-        if( cnt2 > 0 && tid < 32 ) {
-            TileView tv;
-            tv.D = D; tv.tx0 = tx0; tv.ty0 = ty0; tv.cols = EX_SW; tv.rows = EX_SH;
-            tv.g.base = L.base[o]; tv.g.lstride = L.lstride[o]; tv.g.pitch = L.pitch[o]; tv.g.w = w; tv.g.h = h; tv.g.nlvl = n_lvl;
-            tv.g.y_lo = L.row_lo[o]; tv.g.y_hi = L.row_hi[o];
-            tv.w = w; tv.h = h; tv.nlvl = n_lvl;
+        if( tid < 32 ) {
             for( int i = tid; i < cnt2; i += 32 ) {
                 const unsigned e = q2[i];
-                const int x = tx0 + ( e & 63 ), y = ty0 + ( ( e >> 6 ) & 15 ), level = e >> 10;
-                refine_and_append<MODE>( tv, K, o, x, y, level, q2v[i], cand, cand_stride, ct );
+                const int at = n_pend + i;
+                if( at < EX_PEND ) {
+                    pend_xy[at]  = (unsigned)( tx0 + (int)( e & 63 ) ) | ( (unsigned)( ty0 + (int)( ( e >> 6 ) & 15 ) ) << 16 );
+                    pend_lo[at]  = (unsigned)( e >> 10 ) | ( (unsigned)o << 8 );
+                    pend_val[at] = q2v[i];
+                } else {                                                        /* more than the list holds in one tile: at once */
+                    DogView dv;
+                    dv.base = L.base[o]; dv.lstride = L.lstride[o]; dv.pitch = L.pitch[o]; dv.w = w; dv.h = h; dv.nlvl = n_lvl;
+                    dv.y_lo = L.row_lo[o]; dv.y_hi = L.row_hi[o];
+                    refine_and_append<MODE>( dv, K, o, tx0 + (int)( e & 63 ), ty0 + (int)( ( e >> 6 ) & 15 ), (int)( e >> 10 ), q2v[i], cand, cand_stride, ct );
+                }
+            }
+            n_pend = min( n_pend + cnt2, EX_PEND );
+            __syncwarp();
+            while( n_pend >= 32 ) {
+                n_pend -= 32;
+                refine_pending<MODE>( L, K, n_lvl, pend_xy[n_pend + tid], pend_lo[n_pend + tid], pend_val[n_pend + tid], cand, cand_stride, ct );
+                __syncwarp();
             }
         }
         /* no barrier here: the next step uses the other buffer and the other counters, and its own barriers come
          * before anything of this step is overwritten */
     }
+    if( tid < 32 && tid < n_pend )
+        refine_pending<MODE>( L, K, n_lvl, pend_xy[tid], pend_lo[tid], pend_val[tid], cand, cand_stride, ct );
 }
 
 /* Clamp the per-octave counters to max_extrema (s_extrema.cu:555-561), build the prefix sums,
