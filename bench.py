@@ -28,9 +28,9 @@ BATCH = 25            # frames per step per GPU
 N_DISTINCT = 16       # distinct synthetic frames cycled through (seeds 1000..1015)
 IN_FLIGHT = int(os.environ.get("PSIFT_SLOTS", "6"))   # frames in flight = frame slots of the context
 BLUR_DRAM_BYTES = 33.6e6       # dram read+write of one k_blur_march launch (3840x2160 level), ncu --set full: profiles/r02_ncu_blur_march.txt
-PROFILE_SRC = "profiles/r02_ncu_blur_march.txt, profiles/r02h_ncu_frame_summary.txt"
+PROFILE_SRC = "profiles/r02_ncu_blur_march.txt, profiles/r02q_ncu_frame_summary.txt"
 N_PYR_LAUNCHES = 46
-PYR_DRAM_BYTES = 227.6e6       # dram read+write of the 46 pyramid launches of one frame (r02h frame summary + the four octave-0 launches of the march capture)
+PYR_DRAM_BYTES = 227.4e6       # dram read+write of the 46 pyramid launches of one frame (profiles/r02q_ncu_frame_summary.txt)
 REF_REPEATS = 3
 CXX_PRODUCERS = 2     # caller threads per GPU that enqueue() and get() in the C++-class leg
 CXX_WINDOW = 6        # jobs each of them keeps outstanding
