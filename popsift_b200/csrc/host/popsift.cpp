@@ -9,6 +9,10 @@
  * own future.  All CUDA work goes through the C ABI (psift.h).
  */
 #include <popsift/popsift.h>
+#if defined( __x86_64__ ) && defined( __SSE2__ )
+#include <emmintrin.h>
+#endif
+#include <cstdint>
 #include <psift.h>
 
 #include <condition_variable>
@@ -80,12 +84,35 @@ struct PinnedPool {
 PinnedPool& pinned_pool() { static PinnedPool* p = new PinnedPool; return *p; }     /* never torn down: jobs may outlive every PopSift */
 }
 
+/* The private copy of a frame: read once by the DMA engine and never by this CPU again, so it is written with
+ * streaming stores where the machine has them - no read-for-ownership of the destination, no eviction of the caller's
+ * working set (with eight GPUs fed from one host the copies of all workers add up to the memory system's limit). */
+static void copy_image( unsigned char* dst, const void* src_v, size_t n )
+{
+#if defined( __x86_64__ ) && defined( __SSE2__ )
+    const unsigned char* src = (const unsigned char*)src_v;
+    if( n >= ( 256u << 10 ) && ( ( (uintptr_t)dst & 15u ) == 0 ) ) {
+        size_t i = 0;
+        for( ; i + 64 <= n; i += 64 ) {
+            const __m128i a = _mm_loadu_si128( (const __m128i*)( src + i ) ),      b = _mm_loadu_si128( (const __m128i*)( src + i + 16 ) );
+            const __m128i c = _mm_loadu_si128( (const __m128i*)( src + i + 32 ) ), d = _mm_loadu_si128( (const __m128i*)( src + i + 48 ) );
+            _mm_stream_si128( (__m128i*)( dst + i ), a );      _mm_stream_si128( (__m128i*)( dst + i + 16 ), b );
+            _mm_stream_si128( (__m128i*)( dst + i + 32 ), c ); _mm_stream_si128( (__m128i*)( dst + i + 48 ), d );
+        }
+        _mm_sfence();
+        if( i < n ) memcpy( dst + i, src + i, n - i );
+        return;
+    }
+#endif
+    memcpy( dst, src_v, n );
+}
+
 void SiftJob::allocImage( size_t n, const void* src )
 {
     _imageData = (unsigned char*)pinned_pool().get( n );
     _pinned = _imageData != 0;
     if( !_imageData ) _imageData = job_alloc( n );
-    if( _imageData ) memcpy( _imageData, src, n );
+    if( _imageData ) copy_image( _imageData, src, n );
     else std::cerr << "popsift: SiftJob: out of memory for a " << _w << "x" << _h << " image" << std::endl;
 }
 

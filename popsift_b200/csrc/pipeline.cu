@@ -25,6 +25,10 @@
 #include <string>
 #include <cmath>
 #include <new>
+#include <cstdint>
+#if defined( __x86_64__ ) && defined( __SSE2__ )
+#include <emmintrin.h>
+#endif
 
 using namespace psift;
 
@@ -818,10 +822,31 @@ void psift_destroy( psift_ctx* c )
 
 /* rows of a host image into the page-locked staging buffer; large images are copied by several threads (one core moves
  * about 5 GB/s, a 16384 x 16384 image is 268 MB) */
+/* Copy into the page-locked staging block: read once by the DMA engine and never by this CPU again, so large runs are
+ * written with streaming stores (no read-for-ownership of the destination, the caller's working set stays cached). */
+static void stage_copy( char* dst, const char* src, size_t n )
+{
+#if defined( __x86_64__ ) && defined( __SSE2__ )
+    if( n >= ( 256u << 10 ) && ( ( (uintptr_t)dst & 15u ) == 0 ) ) {
+        size_t i = 0;
+        for( ; i + 64 <= n; i += 64 ) {
+            const __m128i a = _mm_loadu_si128( (const __m128i*)( src + i ) ),      b = _mm_loadu_si128( (const __m128i*)( src + i + 16 ) );
+            const __m128i c = _mm_loadu_si128( (const __m128i*)( src + i + 32 ) ), d = _mm_loadu_si128( (const __m128i*)( src + i + 48 ) );
+            _mm_stream_si128( (__m128i*)( dst + i ), a );      _mm_stream_si128( (__m128i*)( dst + i + 16 ), b );
+            _mm_stream_si128( (__m128i*)( dst + i + 32 ), c ); _mm_stream_si128( (__m128i*)( dst + i + 48 ), d );
+        }
+        _mm_sfence();
+        if( i < n ) memcpy( dst + i, src + i, n - i );
+        return;
+    }
+#endif
+    memcpy( dst, src, n );
+}
+
 static void stage_rows( char* dst, size_t dpitch, const char* src, size_t spitch, size_t row_bytes, int nrows )
 {
     auto part = [=]( int y0, int y1 ) {
-        if( spitch == dpitch && y1 > y0 ) memcpy( dst + (size_t)y0 * dpitch, src + (size_t)y0 * spitch, spitch * (size_t)( y1 - y0 - 1 ) + row_bytes );
+        if( spitch == dpitch && y1 > y0 ) stage_copy( dst + (size_t)y0 * dpitch, src + (size_t)y0 * spitch, spitch * (size_t)( y1 - y0 - 1 ) + row_bytes );
         else for( int y = y0; y < y1; y++ ) memcpy( dst + (size_t)y * dpitch, src + (size_t)y * spitch, row_bytes );
     };
     const size_t bytes = row_bytes * (size_t)nrows;
