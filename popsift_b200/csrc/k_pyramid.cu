@@ -668,7 +668,7 @@ static int env_int( const char* name, int dflt )
     const char* e = getenv( name );
     return e ? atoi( e ) : dflt;
 }
-static long march_min_px()   { static long v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH", 1 ) ? (long)env_int( "PSIFT_MARCH_MIN", 3000000 ) : 0x7fffffffffffL; return v; }
+static long march_min_px()   { static long v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH", 1 ) ? (long)env_int( "PSIFT_MARCH_MIN", 2000000 ) : 0x7fffffffffffL; return v; }
 static int  march_wps()      { static int v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH_WPS", 8 ); return v; }
 static bool march_tex()      { static int v = -1; if( v < 0 ) v = env_int( "PSIFT_MARCH_TEX", 1 ); return v != 0; }
 
@@ -693,7 +693,10 @@ static cudaError_t launch_march_rs( const BlurArgs& a, cudaStream_t st )
     /* segments per strip: about march_wps() warps per SM, picked among the neighbouring counts for the fewest steps of
      * the slowest SM (steps of a segment, RS rows each, 2H of warm-up) x (blocks on the fullest SM).  Segments start on
      * even rows (the fused downscale takes even rows). */
-    const int target = std::max( 1, sms * march_wps() / m.nstrip );
+    /* planes under 3 Mpx (octave 1 of a 1080p frame) get fewer, longer segments: alone on the GPU that is no faster than the
+     * tile kernel (too few warps), with other frames' kernels filling the SMs it is 2 % more frames per second */
+    static int wps_small = -1; if( wps_small < 0 ) wps_small = env_int( "PSIFT_MARCH_WPS_SMALL", 6 );
+    const int target = std::max( 1, sms * ( (long)a.w * rows < 3000000L ? wps_small : march_wps() ) / m.nstrip );
     long best = -1;
     for( int n = std::max( 1, target - 3 ); n <= target + 3; n++ ) {
         const int sr = std::max( 32, ( ( rows + n - 1 ) / n + 1 ) / 2 * 2 );
