@@ -107,7 +107,7 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
                     const float dy = __fsub_rn( (float)yy, y );
                     const int sq_dist = (int)__fmaf_rn( dy, dy, __fmul_rn( dx, dx ) );
                     if( sq_dist <= sq_thres ) {
-                        const float grad  = hypotf( gx, gy );
+                        const float grad  = hypot_as_lib( gx, gy );
                         const float theta = atan2f( gy, gx );
                         weight = __fmul_rn( grad, expf( __fmul_rn( (float)sq_dist, factor ) ) );
                         int bidx = (int)roundf( __fdividef( float( ORI_NBINS ) * ( theta + PI_F ), PI2_F ) );
