@@ -264,7 +264,7 @@ def bench_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)      # 200 x 25 frames: a timed region of about 2 s per leg
+    ap.add_argument("--steps", type=int, default=240)      # 240 x 25 frames: a timed region of a little over 2 s per leg
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
