@@ -21,8 +21,11 @@ namespace psift {
 __device__ static const float PI_F  = 3.14159265358979323846f;          /* sift_constants.h:27-36 */
 __device__ static const float PI2_F = 2.0f * 3.14159265358979323846f;
 
-constexpr int ORI_WARPS = 4;
-constexpr int ORI_CH    = 1024;            /* samples per chunk: 32 steps of the reference's 32-thread loop */
+#ifndef PSIFT_ORI_WARPS
+#define PSIFT_ORI_WARPS 4
+#endif
+constexpr int ORI_WARPS = PSIFT_ORI_WARPS;
+constexpr int ORI_CH    = ORI_WARPS >= 4 ? 1024 : 512;            /* samples per chunk: 32 steps of the reference's 32-thread loop */
 
 /* Histogram accumulation in the REFERENCE'S ORDER.  ori_par (s_orientation.cu:104-138) is one warp: sample i is taken by
  * lane i % 32 in step i / 32 and added with a shared-memory float atomicAdd, which compiles to a compare-and-swap loop
@@ -87,7 +90,7 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
         const int wxs = max( wx, 1 );
         const int q32 = 32 / wxs, r32 = 32 - q32 * wxs;                     /* (row, column) advance per step */
 
-        if( tid < ORI_NBINS ) hist[0][tid] = 0.0f;
+        for( int b = tid; b < ORI_NBINS; b += ORI_WARPS * 32 ) hist[0][b] = 0.0f;
         for( int c0 = 0; c0 < loops; c0 += ORI_CH ) {
             const int n_it = min( ORI_CH / 32, ( loops - c0 + 31 ) >> 5 );   /* steps in this chunk */
             const int ipw  = ( n_it + ORI_WARPS - 1 ) / ORI_WARPS;          /* steps per warp: contiguous ranges */
@@ -154,11 +157,11 @@ k_orientation( const __grid_constant__ PyrLayout L, const Cand* __restrict__ can
                 if( key < ORI_NBINS ) lst[wbase[( idx >> 5 ) / ipw][key] + sp[idx]] = sw[idx];
             }
             __syncthreads();
-            if( tid < ORI_NBINS ) {
-                float acc = hist[0][tid];
-                const int j1 = bstart[tid + 1];
-                for( int j = bstart[tid]; j < j1; j++ ) acc = __fadd_rn( acc, lst[j] );
-                hist[0][tid] = acc;
+            for( int b = tid; b < ORI_NBINS; b += ORI_WARPS * 32 ) {
+                float acc = hist[0][b];
+                const int j1 = bstart[b + 1];
+                for( int j = bstart[b]; j < j1; j++ ) acc = __fadd_rn( acc, lst[j] );
+                hist[0][b] = acc;
             }
             __syncthreads();
         }
@@ -326,6 +329,8 @@ k_ori_prefix( psift_extremum* __restrict__ ext, Counters* __restrict__ ct, int* 
         ct->ori_ps[MAX_OCT] = ori_total;
     }
 }
+
+int orientation_blocks_per_sm() { return ORI_WARPS >= 4 ? 10 : ( ORI_WARPS == 2 ? 16 : 28 ); }
 
 cudaError_t launch_orientation( const PyrLayout& L, const Cand* sorted, Counters* ct, psift_extremum* ext,
                                 int* desc_map, DescWork* work, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches )

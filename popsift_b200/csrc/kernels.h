@@ -40,6 +40,7 @@ cudaError_t launch_grid_filter( const PyrLayout& L, const psift_config& cfg, Can
 cudaError_t launch_match( const float* l, int l_len, const float* r, int r_len, int* out3, float* dist2, cudaStream_t st );
 cudaError_t launch_ref_features( const psift_feature* in, int n, float* desc_base, void* out72, cudaStream_t st );
 /* k_orient.cu */
+int orientation_blocks_per_sm();
 cudaError_t launch_orientation( const PyrLayout& L, const Cand* sorted, Counters* ct, psift_extremum* ext,
                                 int* desc_map, DescWork* work, int desc_capacity, int n_blocks, cudaStream_t st, long long* launches );
 /* k_desc.cu */

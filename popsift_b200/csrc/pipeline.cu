@@ -566,7 +566,7 @@ static int enqueue_frame( psift_ctx* c, Slot& s, bool capturing, int parts = FRA
     CU( launch_extrema( L, c->K, s.tmaps_d, s.cand, s.cand_stride, s.sorted, s.sort_tmp, s.ext_cap, s.ct, &reinterpret_cast<CountersAndSort*>( s.ct )->ss, st, &c->launches ) );
     CU( launch_grid_filter( L, c->cfg, s.sorted, s.cand, s.ext_cap, s.ct, s.filt, st, &c->launches ) );
     CU( stamp( s.ev[3] ) );
-    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_work, s.desc_cap, c->n_sm * 10, st, &c->launches ) );
+    CU( launch_orientation( L, s.sorted, s.ct, s.ext, s.desc_map, s.desc_work, s.desc_cap, c->n_sm * orientation_blocks_per_sm(), st, &c->launches ) );
     CU( stamp( s.ev[4] ) );
     CU( launch_descriptors( L, c->K, s.ext, s.ct, s.desc_work, s.lintex_d, c->d_dt, s.desc, s.feat, c->n_sm * 4, st, &c->launches ) );
     CU( stamp( s.ev[5] ) );
